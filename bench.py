@@ -1,0 +1,396 @@
+#!/usr/bin/env python
+"""bench.py -- calibrated frames/s of the psana-ray hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload calib|cm|image|jungfrau] [--impl ours|reference]
+
+A step is one pass of the hot path over one batch of synthetic raw frames (default workload =
+BASELINE.json configs[1]: epix10k2M pedestal + gain-switch calibration, batch 64, one B200).  Prints
+ONE JSON line: the device-resident throughput (`value`), the end-to-end number through the C ABI
+with host buffers (`e2e`), the roofline of the dominant kernel and the CPU baseline (NumPy oracle on
+this box's host cores).  For N > 1 launch with torch.distributed.run, one rank per GPU; events
+shard by rank, there is no data-path collective (weak scaling).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import multiprocessing as mp
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (os.path.join(ROOT, "psana-ray_b200"), ROOT):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np
+
+BATCH = 64
+METRIC = "calibrated epix10k2M frames/sec"
+WORKLOADS = {
+    # name -> (detector, common-mode cmpars, image?, BASELINE.json config it is)
+    "calib":    ("epix10k2M", None, False, "configs[1]: epix10k2M pedestal + gain-switch calibration, batch 64, constants L2-resident"),
+    "cm":       ("epix10k2M", (7, 4, 100.0, 10), False, "configs[2] (calib part): epix10k2M calib + per-bank common-mode median + mask, batch 64"),
+    "image":    ("epix10k2M", (7, 4, 100.0, 10), True, "configs[2]: epix10k2M calib + per-bank common-mode median + mask + assembled image, batch 64"),
+    "image_nocm": ("epix10k2M", None, True, "epix10k2M calib fused with image assembly, batch 64"),
+    "jungfrau": ("jungfrau4M", None, False, "configs[3]: Jungfrau 4M 3-gain-stage calibration, batch 64 per GPU"),
+}
+
+
+# =====================================================================================================
+# CPU reference arm: the NumPy oracle (the reference's own CPU path, psana det.calib, is not installable
+# offline -- see oracle/psana_calib.py), one process per host core like `mpirun -n N`.
+# =====================================================================================================
+
+def _cpu_worker(rank, nprocs, detector, cmpars, image, frames, warm, rounds, barrier, q):
+    from oracle import psana_calib as oc
+    from psana_ray import synthetic as syn
+    spec = syn.detector_spec(detector)
+    consts = syn.make_constants(spec, seed=0)
+    consts["gfac"] = oc.divide_protected(np.ones_like(consts["gain"]), consts["gain"])   # psana caches gfac once per run
+    raw = syn.make_raw_frames(spec, consts, max(1, min(frames, 4)), seed=100 + rank)
+    geo = syn.make_pixel_index_arrays(spec) if image else None
+
+    def one(f):
+        r = raw[f % raw.shape[0]]
+        if image:
+            return oc.det_image(spec.kind, r, consts, geo[0], geo[1], cmpars)
+        return oc.det_calib(spec.kind, r, consts, cmpars)
+
+    for f in range(warm):
+        one(f)
+    spans = []
+    for _ in range(rounds):
+        barrier.wait()
+        t0 = time.perf_counter()
+        for f in range(frames):
+            one(f)
+        t1 = time.perf_counter()
+        spans.append((t0, t1))
+    q.put((rank, spans))
+
+
+def run_cpu_reference(detector, cmpars, image, nprocs, frames_per_proc, rounds, warm=1):
+    """Returns list of per-round wall seconds for nprocs*frames_per_proc frames."""
+    ctx = mp.get_context("fork")
+    barrier = ctx.Barrier(nprocs)
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_cpu_worker, args=(r, nprocs, detector, cmpars, image, frames_per_proc, warm, rounds, barrier, q))
+             for r in range(nprocs)]
+    for p in procs:
+        p.start()
+    res = [q.get() for _ in procs]
+    for p in procs:
+        p.join()
+    walls = []
+    for i in range(rounds):
+        t0 = min(s[i][0] for _, s in res)
+        t1 = max(s[i][1] for _, s in res)
+        walls.append(t1 - t0)
+    return walls
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+# =====================================================================================================
+# clocks
+# =====================================================================================================
+
+class ClockSampler:
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+               0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting", 0x100: "display_clock_setting"}
+
+    def __init__(self, index):
+        self.samples = []
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                mhz = self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)
+                try:
+                    rs = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    rs = self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.samples.append((time.perf_counter(), mhz, rs))
+            except Exception:
+                pass
+            time.sleep(0.002)
+
+    def start(self):
+        if self.nv is not None:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thr is not None:
+            self._thr.join()
+
+    def summary(self, t0, t1):
+        if self.nv is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "note": "NVML unavailable"}
+        inside = [s for s in self.samples if t0 <= s[0] <= t1]
+        note = "timed region"
+        if len(inside) < 3:
+            inside = [s for s in self.samples if s[0] >= t0]
+            note = "timed region + probe loop under the same load"
+        mhz = sorted(s[1] for s in inside)
+        bits = 0
+        for s in inside:
+            bits |= s[2]
+        reasons = sorted({name for b, name in self.REASONS.items() if bits & b})
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": self.max_mhz, "reasons": reasons,
+                "samples": len(inside), "sampled": note}
+
+
+# =====================================================================================================
+
+def algorithmic_bytes_per_frame(spec, image_shape):
+    """2 B raw in + 4 B float out per pixel (image mode: 2 B x npix in + 4 B x H x W out)."""
+    if image_shape is not None:
+        return 2 * spec.npix + 4 * image_shape[0] * image_shape[1]
+    return 6 * spec.npix
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as fh:
+            d = json.load(fh)
+        return float(d["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured copy bandwidth)"
+    except Exception:
+        return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+
+
+def ncu_traffic(workload):
+    """dram bytes per launch of the dominant kernel from the committed ncu capture, or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as fh:
+            return json.load(fh).get(workload)
+    except Exception:
+        return None
+
+
+def reference_arm(args, rank, world):
+    if rank != 0:
+        return 0
+    detector, cmpars, image, cfgname = WORKLOADS[args.workload]
+    nprocs = args.cpu_procs or host_cores()
+    fpp = args.cpu_frames_per_proc
+    walls = run_cpu_reference(detector, cmpars, image, nprocs, fpp, rounds=args.warmup + args.steps, warm=1)
+    timed = walls[args.warmup:]
+    total = sum(timed)
+    frames_per_step = nprocs * fpp
+    value = frames_per_step * len(timed) / total
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(timed),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": cfgname, "detector": detector, "frames_per_step": frames_per_step,
+                   "note": "reference CPU path = NumPy restatement of psana det.calib (psana/ray/mpi4py not installable offline); "
+                           "one process per host core, mirroring mpirun -n N"},
+        "cpu_baseline": {"value": value, "unit": "frames/s", "cores": nprocs, "kind": "port",
+                         "sample": f"{frames_per_step} frames per step ({fpp} per process), {len(timed)} timed steps"},
+        "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--workload", choices=sorted(WORKLOADS), default="calib")
+    ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--frames-per-block", type=int, default=0)
+    ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 20)")
+    ap.add_argument("--cpu-procs", type=int, default=0, help="CPU reference processes (0 = all host cores)")
+    ap.add_argument("--cpu-frames-per-proc", type=int, default=4)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        return reference_arm(args, rank, world)
+
+    detector, cmpars, image, cfgname = WORKLOADS[args.workload]
+
+    # ---- CPU baseline first (fork before CUDA is initialised); rank 0 at N = 1 only ---------------
+    cpu_baseline = None
+    if world == 1 and not args.no_cpu_baseline:
+        nprocs = min(args.cpu_procs or host_cores(), 32)
+        fpp = 8
+        walls = run_cpu_reference(detector, cmpars, image, nprocs, fpp, rounds=2, warm=1)
+        cpu_baseline = {"value": nprocs * fpp / walls[-1], "unit": "frames/s", "cores": nprocs, "kind": "port",
+                        "sample": f"{nprocs} processes x {fpp} frames of the same workload (NumPy oracle), second of two rounds; "
+                                  f"host has {host_cores()} usable cores",
+                        "frames_per_sec_per_core": fpp / walls[-1]}
+
+    import torch
+    import torch.distributed as dist
+    from psana_ray import synthetic as syn
+    from psana_ray.calib import GpuCalibrator
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device; there is no CPU fallback (use --impl reference for the CPU arm)")
+    dev = local_rank % torch.cuda.device_count()
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", dev))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    spec = syn.detector_spec(detector)
+    consts = syn.make_constants(spec, seed=0)
+    B = args.batch
+    raw = syn.make_raw_frames(spec, consts, min(B, 16), seed=1000 + rank)
+    if raw.shape[0] < B:      # tile 16 distinct frames and perturb the ADC bits so every frame differs
+        reps = (B + raw.shape[0] - 1) // raw.shape[0]
+        raw = np.concatenate([raw] * reps)[:B].copy()
+        raw[16:] ^= (np.arange(B - 16, dtype=np.uint16) * 37 % 512 + 1)[:, None, None, None]
+    cal = GpuCalibrator(spec, device=dev)
+    cal.set_constants(consts["peds"], consts.get("gain"), consts.get("offs"), consts.get("cfg"), consts.get("mask"))
+    cal.set_common_mode(cmpars)
+    image_shape = None
+    if image:
+        image_shape = cal.set_geometry(*syn.make_pixel_index_arrays(spec))
+        cal.reserve(B)
+    if args.frames_per_block:
+        cal.set_option("frames_per_block", args.frames_per_block)
+
+    h_raw = torch.from_numpy(raw.view(np.int16)).pin_memory()
+    d_raw = h_raw.cuda(non_blocking=True)
+    d_out = torch.empty(cal.out_shape(B, image), dtype=torch.float32, device="cuda")
+    h_out = torch.empty(cal.out_shape(B, image), dtype=torch.float32).pin_memory()
+    stream = torch.cuda.current_stream()
+    launches_per_step = 2 if (image and cmpars is not None) else 1
+
+    # ---- device-resident throughput ---------------------------------------------------------------
+    sampler = ClockSampler(dev)
+    for _ in range(args.warmup):
+        cal.calib(d_raw, out=d_out, image=image)
+    barrier()
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    sampler.start()
+    t_wall0 = time.perf_counter()
+    evs[0].record(stream)
+    for i in range(args.steps):
+        cal.calib(d_raw, out=d_out, image=image)
+        evs[i + 1].record(stream)
+    barrier()
+    t_wall1 = time.perf_counter()
+    total_ms = evs[0].elapsed_time(evs[-1])
+    step_ms = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
+    if len([s for s in sampler.samples if t_wall0 <= s[0] <= t_wall1]) < 3:     # short region: probe the clocks under the same load
+        t_end = time.perf_counter() + 0.25
+        while time.perf_counter() < t_end:
+            for _ in range(20):
+                cal.calib(d_raw, out=d_out, image=image)
+            torch.cuda.synchronize()
+    sampler.stop()
+    clocks = sampler.summary(t_wall0, t_wall1)
+    t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms_max = float(t.item())
+    value = world * B * args.steps / (total_ms_max / 1e3)
+
+    # ---- end to end through the C ABI with host buffers: H2D of raw + calib + D2H of the result ----
+    e2e_steps = args.e2e_steps or min(args.steps, 20)
+    for _ in range(3):
+        cal.calib_host(h_raw, h_out=h_out, image=image)
+    barrier()
+    tw0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        cal.calib_host(h_raw, h_out=h_out, image=image)      # synchronous: returns when h_out is final
+    barrier()
+    e2e_s = time.perf_counter() - tw0     # the call blocks on the library's own streams, so the host clock brackets the device work
+    t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * B * e2e_steps / float(t.item())
+    # device-resident output variant (the CUDA-IPC hand-off design: results stay on the GPU)
+    for _ in range(2):
+        cal.calib_host(h_raw, d_out=d_out, image=image)
+    barrier()
+    tw0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        cal.calib_host(h_raw, d_out=d_out, image=image)
+    barrier()
+    t = torch.tensor([time.perf_counter() - tw0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_dev_value = world * B * e2e_steps / float(t.item())
+
+    # ---- roofline of the dominant kernel (one launch = one step's batch) ------------------------------
+    peak, peak_src = measured_peaks()
+    alg_bytes = algorithmic_bytes_per_frame(spec, image_shape) * B
+    avg_launch_s = (sum(step_ms) / len(step_ms)) / 1e3
+    achieved = alg_bytes / avg_launch_s / 1e9
+    pcie_peak = 63.0
+    h2d_bytes = raw.nbytes
+    d2h_bytes = h_out.numel() * 4
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": cfgname, "detector": spec.name, "frame_shape": list(spec.shape), "batch_per_gpu": B,
+                       "common_mode": list(cmpars) if cmpars else None, "image": image_shape,
+                       "sharding": "events by rank, no collective" if world > 1 else "single GPU",
+                       "l2": f"inputs larger than L2: {raw.nbytes / 1e6:.0f} MB raw in + {d_out.numel() * 4 / 1e6:.0f} MB out per step vs 126 MB L2",
+                       "seed": 1000},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": ncu_traffic(args.workload), "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_ms": avg_launch_s * 1e3,
+                         "min_launch_ms": min(step_ms), "kernel_launches_per_step": launches_per_step},
+            "cpu_baseline": cpu_baseline,
+            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
+                    "steps": e2e_steps, "path": "psr_calib_batch_host: pinned host raw -> H2D chunks on a side stream -> kernels -> D2H to pinned host",
+                    "pcie_frac_of_63GBs": {"h2d": e2e_value / world * (h2d_bytes / B) / 1e9 / pcie_peak,
+                                           "d2h": e2e_value / world * (d2h_bytes / B) / 1e9 / pcie_peak},
+                    "device_resident_out": {"value": e2e_dev_value, "unit": "frames/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 0,
+                                            "pcie_frac_of_63GBs_h2d": e2e_dev_value / world * (h2d_bytes / B) / 1e9 / pcie_peak,
+                                            "note": "calibrated batch stays on the GPU for CUDA-IPC hand-off to same-box consumers"}},
+            "gpu_launches": args.steps * launches_per_step,
+            "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,329 @@
+// calib_map.cu -- streaming calibration kernels for sm_100a (no common mode):
+//   K1 epix10ka  : gain-bit decode + pedestal + gain + mask          (calib_epix10ka_any)
+//   K2 jungfrau  : gain-bit decode + pedestal + offset + gain + mask (calib_jungfrau,     BASELINE.md 2.3)
+//   K5 masks     : np.where(keep, data, 0) of producer.py:92-95, folded into the epilogues
+//   K4 assemble  : det.image as a gather through the inverse geometry map, either
+//                  fused with K1/K2 (raw -> image directly) or from an already calibrated batch
+//   decode       : gain-mode index per pixel, for bit-exact checking of the decode
+//
+// Design: HBM-bound streaming map.  Work is pixel-tile-major, frames-inner: a thread owns a few
+// pixels, loads their per-run constants ONCE into registers and then walks the frames of the batch,
+// so HBM traffic per frame is raw-in (2 B/px) + float-out (4 B/px); the constants cost
+// size/frames_per_block per frame and come from L2 when they fit (epix10ka 36.8 MB).  Raw loads and
+// output stores carry streaming (evict-first) hints so they do not push the constants out of L2.
+// Every float op is an explicit round-to-nearest intrinsic: NumPy does subtract, multiply, multiply
+// as separate ufunc passes, so no FMA contraction and no re-association is allowed.
+#include "psr_kernels.cuh"
+
+namespace {
+
+constexpr int MAP_THREADS = 256;
+constexpr int MAP_UNROLL = 4;       // frames in flight per thread
+
+__device__ __forceinline__ float maskf(uint32_t flbyte) { return (flbyte & PSR_FL_MASK) ? 1.0f : 0.0f; }
+
+// ---- one epix10ka pixel -------------------------------------------------------------------------
+__device__ __forceinline__ float epix_px(uint32_t v, float p0, float g0, float p1, float g1, uint32_t fl) {
+    const bool sw = (v & 0x4000u) != 0;                         // data bit 14 -> table entry
+    const float x = (float)(v & 0x3FFFu);
+    float o = __fmul_rn(__fmul_rn(__fsub_rn(x, sw ? p1 : p0), sw ? g1 : g0), maskf(fl));
+    return (fl & PSR_FL_KEEP) ? o : 0.0f;
+}
+
+// ---- one jungfrau pixel -------------------------------------------------------------------------
+template <bool HAS_OFFS>
+__device__ __forceinline__ float jf_px(uint32_t v, const float* p, const float* o, const float* g, uint32_t fl) {
+    const uint32_t gb = v >> 14;                                 // 00 g0, 01 g1, 11 g2, 10 none
+    float x = (float)(v & 0x3FFFu);
+    float ped = 0.0f, off = 0.0f, gf = 1.0f;
+    if (gb == 0)      { ped = p[0]; gf = g[0]; if (HAS_OFFS) off = o[0]; }
+    else if (gb == 1) { ped = p[1]; gf = g[1]; if (HAS_OFFS) off = o[1]; }
+    else if (gb == 3) { ped = p[2]; gf = g[2]; if (HAS_OFFS) off = o[2]; }
+    x = __fsub_rn(x, ped);                                       // arrf[gr] -= peds[i][gr]   (x - 0 is exact)
+    if (HAS_OFFS) x = __fsub_rn(x, off);                         // arrf -= offset, separately rounded
+    float r = __fmul_rn(__fmul_rn(x, gf), maskf(fl));
+    return (fl & PSR_FL_KEEP) ? r : 0.0f;
+}
+
+__device__ __forceinline__ float f4get(const float4& v, int i) { return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w; }
+
+// =================================================================================================
+// K1: epix10ka calib map.  A warp covers 64 groups of 4 pixels; lane L owns groups L and L+32 so
+// that both the 8-byte raw loads and the 16-byte output stores of a warp instruction are contiguous.
+// =================================================================================================
+__global__ void __launch_bounds__(MAP_THREADS)
+epix_calib_map_kernel(const uint2* __restrict__ raw, float4* __restrict__ out,
+                      const float4* __restrict__ ped0, const float4* __restrict__ gf0,
+                      const float4* __restrict__ ped1, const float4* __restrict__ gf1,
+                      const uint32_t* __restrict__ flags, int ngroups, int nframes, int fpb)
+{
+    const int lane = threadIdx.x & 31;
+    const int wbase = (blockIdx.x * MAP_THREADS + (threadIdx.x & ~31)) * 2;
+    const int g0i = wbase + lane, g1i = wbase + 32 + lane;
+    const bool ok0 = g0i < ngroups, ok1 = g1i < ngroups;
+    if (!ok0) return;
+    const int f_begin = blockIdx.y * fpb;
+    const int f_end = min(nframes, f_begin + fpb);
+
+    float4 p0[2], q0[2], p1[2], q1[2]; uint32_t fl[2];
+    p0[0] = __ldg(ped0 + g0i); q0[0] = __ldg(gf0 + g0i); p1[0] = __ldg(ped1 + g0i); q1[0] = __ldg(gf1 + g0i); fl[0] = __ldg(flags + g0i);
+    if (ok1) { p0[1] = __ldg(ped0 + g1i); q0[1] = __ldg(gf0 + g1i); p1[1] = __ldg(ped1 + g1i); q1[1] = __ldg(gf1 + g1i); fl[1] = __ldg(flags + g1i); }
+    else     { p0[1] = p0[0]; q0[1] = q0[0]; p1[1] = p1[0]; q1[1] = q1[0]; fl[1] = fl[0]; }
+    const int gi[2] = {g0i, ok1 ? g1i : g0i};
+
+    for (int f = f_begin; f < f_end; f += MAP_UNROLL) {
+        uint2 r[MAP_UNROLL][2];
+#pragma unroll
+        for (int u = 0; u < MAP_UNROLL; ++u) {
+            if (f + u < f_end) {
+                const size_t base = (size_t)(f + u) * ngroups;
+                r[u][0] = __ldcs(raw + base + gi[0]);
+                r[u][1] = __ldcs(raw + base + gi[1]);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < MAP_UNROLL; ++u) {
+            if (f + u < f_end) {
+                const size_t base = (size_t)(f + u) * ngroups;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    if (h == 1 && !ok1) break;
+                    const uint32_t a = r[u][h].x, b = r[u][h].y;
+                    float4 o;
+                    o.x = epix_px(a & 0xFFFFu, p0[h].x, q0[h].x, p1[h].x, q1[h].x, fl[h]);
+                    o.y = epix_px(a >> 16,     p0[h].y, q0[h].y, p1[h].y, q1[h].y, fl[h] >> 8);
+                    o.z = epix_px(b & 0xFFFFu, p0[h].z, q0[h].z, p1[h].z, q1[h].z, fl[h] >> 16);
+                    o.w = epix_px(b >> 16,     p0[h].w, q0[h].w, p1[h].w, q1[h].w, fl[h] >> 24);
+                    __stcs(out + base + gi[h], o);
+                }
+            }
+        }
+    }
+}
+
+// =================================================================================================
+// K2: jungfrau calib map.  One group of 4 pixels per thread (9 float4 of constants = 36 registers).
+// =================================================================================================
+template <bool HAS_OFFS>
+__global__ void __launch_bounds__(MAP_THREADS)
+jf_calib_map_kernel(const uint2* __restrict__ raw, float4* __restrict__ out,
+                    const float4* __restrict__ peds, const float4* __restrict__ offs, const float4* __restrict__ gfac,
+                    const uint32_t* __restrict__ flags, int ngroups, int nframes, int fpb)
+{
+    const int g = blockIdx.x * MAP_THREADS + threadIdx.x;
+    if (g >= ngroups) return;
+    const int f_begin = blockIdx.y * fpb;
+    const int f_end = min(nframes, f_begin + fpb);
+    float P[4][3], O[4][3], G[4][3];
+#pragma unroll
+    for (int m = 0; m < 3; ++m) {
+        const float4 p = __ldg(peds + (size_t)m * ngroups + g);
+        const float4 q = __ldg(gfac + (size_t)m * ngroups + g);
+        float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (HAS_OFFS) o = __ldg(offs + (size_t)m * ngroups + g);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { P[i][m] = f4get(p, i); G[i][m] = f4get(q, i); O[i][m] = f4get(o, i); }
+    }
+    const uint32_t fl = __ldg(flags + g);
+
+    for (int f = f_begin; f < f_end; f += MAP_UNROLL) {
+        uint2 r[MAP_UNROLL];
+#pragma unroll
+        for (int u = 0; u < MAP_UNROLL; ++u)
+            if (f + u < f_end) r[u] = __ldcs(raw + (size_t)(f + u) * ngroups + g);
+#pragma unroll
+        for (int u = 0; u < MAP_UNROLL; ++u) {
+            if (f + u < f_end) {
+                float4 o;
+                o.x = jf_px<HAS_OFFS>(r[u].x & 0xFFFFu, P[0], O[0], G[0], fl);
+                o.y = jf_px<HAS_OFFS>(r[u].x >> 16,     P[1], O[1], G[1], fl >> 8);
+                o.z = jf_px<HAS_OFFS>(r[u].y & 0xFFFFu, P[2], O[2], G[2], fl >> 16);
+                o.w = jf_px<HAS_OFFS>(r[u].y >> 16,     P[3], O[3], G[3], fl >> 24);
+                __stcs(out + (size_t)(f + u) * ngroups + g, o);
+            }
+        }
+    }
+}
+
+// =================================================================================================
+// decode: gain-mode index per pixel
+// =================================================================================================
+__global__ void __launch_bounds__(MAP_THREADS)
+decode_kernel(const uint16_t* __restrict__ raw, uint8_t* __restrict__ modes_out, const uint8_t* __restrict__ modes,
+              int det_kind, int npix, size_t total)
+{
+    const size_t i = (size_t)blockIdx.x * MAP_THREADS + threadIdx.x;
+    if (i >= total) return;
+    const uint32_t v = raw[i];
+    uint32_t m;
+    if (det_kind == 0) {
+        const uint32_t mm = modes[i % npix];
+        m = (v & 0x4000u) ? (mm >> 4) : (mm & 0xFu);
+        if (m == 0xFu) m = 255u;
+    } else {
+        const uint32_t gb = v >> 14;
+        m = gb == 0 ? 0u : gb == 1 ? 1u : gb == 3 ? 2u : 255u;
+    }
+    modes_out[i] = (uint8_t)m;
+}
+
+// =================================================================================================
+// K4: image assembly as a gather.  Output tile = 64 px x 16 rows per CTA (thread = 4 px of one row)
+// so that panels rotated by 90/270 degrees, whose image rows run along detector columns, still use
+// whole 32-byte sectors of the source within one CTA.  VEC = W % 4 == 0 (16-byte stores).
+// =================================================================================================
+constexpr int IMG_TW = 64, IMG_TH = 16;
+
+struct ImgGeom { int H, W; };
+
+template <bool VEC>
+__device__ __forceinline__ void img_store(float* __restrict__ img, size_t off, int ncol, const float v[4]) {
+    if (VEC) { __stcs(reinterpret_cast<float4*>(img + off), make_float4(v[0], v[1], v[2], v[3])); }
+    else { for (int i = 0; i < ncol; ++i) __stcs(img + off + i, v[i]); }
+}
+
+// from an already calibrated batch (common mode on): out[f][p] = src < 0 ? 0 : calib[f][src]
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+image_gather_kernel(const float* __restrict__ calib, float* __restrict__ img, const int32_t* __restrict__ inv,
+                    const uint8_t* __restrict__ keep, int H, int W, int npix, int nframes)
+{
+    const int x0 = blockIdx.x * IMG_TW + (threadIdx.x & 15) * 4;
+    const int y = blockIdx.y * IMG_TH + (threadIdx.x >> 4);
+    if (y >= H || x0 >= W) return;
+    const int ncol = min(4, W - x0);
+    const size_t p0 = (size_t)y * W + x0;
+    int src[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        src[i] = (i < ncol) ? __ldg(inv + p0 + i) : -1;
+        if (keep != nullptr && i < ncol && !__ldg(keep + p0 + i)) src[i] = -1;
+    }
+    const size_t fimg = (size_t)H * W;
+    for (int f = blockIdx.z; f < nframes; f += gridDim.z) {
+        float v[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) v[i] = src[i] >= 0 ? __ldg(calib + (size_t)f * npix + src[i]) : 0.0f;
+        img_store<VEC>(img, (size_t)f * fimg + p0, ncol, v);
+    }
+}
+
+// fused raw -> image (no common mode): constants gathered once per output pixel, frames inner
+template <int DET, bool HAS_OFFS, bool VEC>
+__global__ void __launch_bounds__(256)
+image_fused_kernel(const uint16_t* __restrict__ raw, float* __restrict__ img, PsrDev c, int nframes, int fpb)
+{
+    const int x0 = blockIdx.x * IMG_TW + (threadIdx.x & 15) * 4;
+    const int y = blockIdx.y * IMG_TH + (threadIdx.x >> 4);
+    if (y >= c.H || x0 >= c.W) return;
+    const int ncol = min(4, c.W - x0);
+    const size_t p0 = (size_t)y * c.W + x0;
+    const int f_begin = blockIdx.z * fpb;
+    const int f_end = min(nframes, f_begin + fpb);
+    int src[4]; uint32_t fl[4];
+    float A[4][3], B[4][3], G[4][3];   // epix: A = {ped0, ped1}, G = {gf0, gf1}; jungfrau: A peds, B offs, G gfac
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        int s = (i < ncol) ? __ldg(c.inv + p0 + i) : -1;
+        if (c.keep_image != nullptr && i < ncol && !__ldg(c.keep_image + p0 + i)) s = -1;
+        src[i] = s;
+        const int q = s < 0 ? 0 : s;
+        fl[i] = __ldg(c.flags + q) | PSR_FL_KEEP;     // calib-layout keep mask does not apply to images
+        if (DET == 0) {
+            A[i][0] = __ldg(c.ped0 + q); A[i][1] = __ldg(c.ped1 + q); A[i][2] = 0.f;
+            G[i][0] = __ldg(c.gf0 + q);  G[i][1] = __ldg(c.gf1 + q);  G[i][2] = 0.f;
+            B[i][0] = B[i][1] = B[i][2] = 0.f;
+        } else {
+#pragma unroll
+            for (int m = 0; m < 3; ++m) {
+                A[i][m] = __ldg(c.peds + (size_t)m * c.npix + q);
+                G[i][m] = __ldg(c.gfac + (size_t)m * c.npix + q);
+                B[i][m] = HAS_OFFS ? __ldg(c.offs + (size_t)m * c.npix + q) : 0.f;
+            }
+        }
+    }
+    const size_t fimg = (size_t)c.H * c.W;
+    for (int f = f_begin; f < f_end; ++f) {
+        const uint16_t* rf = raw + (size_t)f * c.npix;
+        uint32_t r[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) r[i] = src[i] >= 0 ? (uint32_t)__ldg(rf + src[i]) : 0u;
+        float v[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float o;
+            if (DET == 0) o = epix_px(r[i], A[i][0], G[i][0], A[i][1], G[i][1], fl[i]);
+            else          o = jf_px<HAS_OFFS>(r[i], A[i], B[i], G[i], fl[i]);
+            v[i] = src[i] >= 0 ? o : 0.0f;
+        }
+        img_store<VEC>(img, (size_t)f * fimg + p0, ncol, v);
+    }
+}
+
+}  // namespace
+
+// ---- launchers --------------------------------------------------------------------------------
+cudaError_t psr_launch_calib_map(const PsrDev& c, const uint16_t* d_raw, int nframes, float* d_out,
+                                 int fpb, cudaStream_t st)
+{
+    if (nframes <= 0) return cudaSuccess;
+    const int ngroups = c.npix / 4;
+    if (fpb <= 0 || fpb > nframes) fpb = nframes;
+    const int ysplit = (nframes + fpb - 1) / fpb;
+    if (c.det_kind == 0) {
+        dim3 grid((ngroups + 2 * MAP_THREADS - 1) / (2 * MAP_THREADS), ysplit);
+        epix_calib_map_kernel<<<grid, MAP_THREADS, 0, st>>>(
+            reinterpret_cast<const uint2*>(d_raw), reinterpret_cast<float4*>(d_out),
+            reinterpret_cast<const float4*>(c.ped0), reinterpret_cast<const float4*>(c.gf0),
+            reinterpret_cast<const float4*>(c.ped1), reinterpret_cast<const float4*>(c.gf1),
+            reinterpret_cast<const uint32_t*>(c.flags), ngroups, nframes, fpb);
+    } else {
+        dim3 grid((ngroups + MAP_THREADS - 1) / MAP_THREADS, ysplit);
+        if (c.offs != nullptr)
+            jf_calib_map_kernel<true><<<grid, MAP_THREADS, 0, st>>>(
+                reinterpret_cast<const uint2*>(d_raw), reinterpret_cast<float4*>(d_out),
+                reinterpret_cast<const float4*>(c.peds), reinterpret_cast<const float4*>(c.offs),
+                reinterpret_cast<const float4*>(c.gfac), reinterpret_cast<const uint32_t*>(c.flags), ngroups, nframes, fpb);
+        else
+            jf_calib_map_kernel<false><<<grid, MAP_THREADS, 0, st>>>(
+                reinterpret_cast<const uint2*>(d_raw), reinterpret_cast<float4*>(d_out),
+                reinterpret_cast<const float4*>(c.peds), nullptr,
+                reinterpret_cast<const float4*>(c.gfac), reinterpret_cast<const uint32_t*>(c.flags), ngroups, nframes, fpb);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t psr_launch_decode(const PsrDev& c, const uint16_t* d_raw, int nframes, uint8_t* d_modes, cudaStream_t st)
+{
+    if (nframes <= 0) return cudaSuccess;
+    const size_t total = (size_t)nframes * c.npix;
+    const unsigned blocks = (unsigned)((total + MAP_THREADS - 1) / MAP_THREADS);
+    decode_kernel<<<blocks, MAP_THREADS, 0, st>>>(d_raw, d_modes, c.modes, c.det_kind, c.npix, total);
+    return cudaGetLastError();
+}
+
+cudaError_t psr_launch_image_gather(const PsrDev& c, const float* d_calib, int nframes, float* d_img, cudaStream_t st)
+{
+    if (nframes <= 0) return cudaSuccess;
+    dim3 grid((c.W + IMG_TW - 1) / IMG_TW, (c.H + IMG_TH - 1) / IMG_TH, min(nframes, 8));
+    if (c.W % 4 == 0)
+        image_gather_kernel<true><<<grid, 256, 0, st>>>(d_calib, d_img, c.inv, c.keep_image, c.H, c.W, c.npix, nframes);
+    else
+        image_gather_kernel<false><<<grid, 256, 0, st>>>(d_calib, d_img, c.inv, c.keep_image, c.H, c.W, c.npix, nframes);
+    return cudaGetLastError();
+}
+
+cudaError_t psr_launch_image_fused(const PsrDev& c, const uint16_t* d_raw, int nframes, float* d_img,
+                                   int fpb, cudaStream_t st)
+{
+    if (nframes <= 0) return cudaSuccess;
+    if (fpb <= 0 || fpb > nframes) fpb = nframes;
+    dim3 grid((c.W + IMG_TW - 1) / IMG_TW, (c.H + IMG_TH - 1) / IMG_TH, (nframes + fpb - 1) / fpb);
+    const bool vec = (c.W % 4 == 0);
+#define PSR_IMG_LAUNCH(DET, OFFS, VEC) image_fused_kernel<DET, OFFS, VEC><<<grid, 256, 0, st>>>(d_raw, d_img, c, nframes, fpb)
+    if (c.det_kind == 0) { if (vec) PSR_IMG_LAUNCH(0, false, true); else PSR_IMG_LAUNCH(0, false, false); }
+    else if (c.offs != nullptr) { if (vec) PSR_IMG_LAUNCH(1, true, true); else PSR_IMG_LAUNCH(1, true, false); }
+    else { if (vec) PSR_IMG_LAUNCH(1, false, true); else PSR_IMG_LAUNCH(1, false, false); }
+#undef PSR_IMG_LAUNCH
+    return cudaGetLastError();
+}

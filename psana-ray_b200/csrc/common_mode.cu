@@ -1,0 +1,324 @@
+// common_mode.cu -- K3: calibration with common-mode correction in ONE pass over HBM (sm_100a).
+//
+// psana applies the common-mode bit word in the order 4 (2-d median per bank per half), 1 (row
+// medians per bank), 2 (column medians per half) on arrf = float(raw & 0x3fff) - ped [- offset],
+// over common-mode-eligible pixels only, before gain and mask (UtilsCommonMode.py; BASELINE.md
+// 2.2-2.4).  All three sub-modes are confined to one "bank-half" tile -- (rows/2) x (cols/nbanks)
+// pixels: 176 x 48 for epix10ka, 256 x 64 for jungfrau -- so one CTA owns one tile of one frame,
+// keeps it in shared memory, runs the enabled sub-modes there and streams the result out.  HBM
+// traffic stays at raw-in + float-out; the constants of the tile come from L2.
+//
+// The median must be EXACT (NumPy: mean of the two middle order statistics, in float32).  Values
+// are mapped to order-preserving uint32 keys and the k-th smallest key is found by a most-
+// significant-bit-first search on count(key < candidate): 32 counting steps, data-independent,
+// no sorting and no atomics.  The 2-d median counts across the CTA (keys live in registers,
+// one barrier per step); row and column medians are done by one warp per line with shuffles.
+#include "psr_kernels.cuh"
+
+namespace {
+
+constexpr uint32_t KEY_INELIGIBLE = 0xFFFFFFFFu;   // key of no finite float
+
+// eight consecutive floats (32-byte aligned source) into registers
+__device__ __forceinline__ void ld8(const float* __restrict__ p, float (&d)[8]) {
+    const float4 u = __ldg(reinterpret_cast<const float4*>(p));
+    const float4 v = __ldg(reinterpret_cast<const float4*>(p) + 1);
+    d[0] = u.x; d[1] = u.y; d[2] = u.z; d[3] = u.w; d[4] = v.x; d[5] = v.y; d[6] = v.z; d[7] = v.w;
+}
+
+template <int NW>
+struct BlockRed {
+    int* buf;      // [2][32]
+    int phase;
+    __device__ __forceinline__ int sum(int v) {
+        v = __reduce_add_sync(0xFFFFFFFFu, v);
+        if ((threadIdx.x & 31) == 0) buf[phase * 32 + (threadIdx.x >> 5)] = v;
+        __syncthreads();
+        int t = 0;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) t += buf[phase * 32 + w];
+        phase ^= 1;
+        return t;
+    }
+    __device__ __forceinline__ uint32_t minu(uint32_t v) {
+        v = __reduce_min_sync(0xFFFFFFFFu, v);
+        if ((threadIdx.x & 31) == 0) buf[phase * 32 + (threadIdx.x >> 5)] = (int)v;
+        __syncthreads();
+        uint32_t t = 0xFFFFFFFFu;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) t = min(t, (uint32_t)buf[phase * 32 + w]);
+        phase ^= 1;
+        return t;
+    }
+};
+
+// k-th smallest (0-based) of the keys held by one warp, NK keys per lane; ineligible keys are
+// KEY_INELIGIBLE and never counted.
+template <int NK>
+__device__ __forceinline__ uint32_t warp_kth(const uint32_t (&key)[NK], int k) {
+    uint32_t prefix = 0;
+#pragma unroll 1
+    for (int bit = 31; bit >= 0; --bit) {
+        const uint32_t cand = prefix | (1u << bit);
+        int c = 0;
+#pragma unroll
+        for (int i = 0; i < NK; ++i) c += (key[i] < cand);
+        c = __reduce_add_sync(0xFFFFFFFFu, c);
+        if (c <= k) prefix = cand;
+    }
+    return prefix;
+}
+
+// median of the eligible keys of one warp (n of them, n >= 1)
+template <int NK>
+__device__ __forceinline__ float warp_median(const uint32_t (&key)[NK], int n) {
+    const int k1 = (n - 1) >> 1, k2 = n >> 1;
+    const uint32_t lo = warp_kth<NK>(key, k1);
+    uint32_t hi = lo;
+    if (k2 != k1) {
+        int cle = 0; uint32_t mg = 0xFFFFFFFFu;
+#pragma unroll
+        for (int i = 0; i < NK; ++i) { cle += (key[i] <= lo); if (key[i] > lo) mg = min(mg, key[i]); }
+        cle = __reduce_add_sync(0xFFFFFFFFu, cle);
+        mg = __reduce_min_sync(0xFFFFFFFFu, mg);
+        if (cle <= k2) hi = mg;                       // the (k2)-th is the next distinct value
+    }
+    return psr_mid(psr_key2f(lo), psr_key2f(hi));
+}
+
+// smem flag byte of a tile pixel: bit0 mask, bit1 eligible (this frame), bit3 keep, bits 4-5 gain selector
+//   epix10ka selector: data bit 14;  jungfrau selector: 0,1,2 = g0,g1,g2, 3 = none
+template <int DET, int ROWS, int COLS, int NB, int NT>
+__global__ void __launch_bounds__(NT)
+cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c)
+{
+    constexpr int TR = ROWS / 2, TC = COLS / NB, CH = TC / 8, NCH = TR * CH, CPT = NCH / NT;
+    constexpr int ST = TC + 1;                       // padded row stride: column walks hit 32 banks
+    constexpr int NW = NT / 32;
+    static_assert(NCH % NT == 0 && NT % 32 == 0, "tile must split evenly over the CTA");
+    extern __shared__ float smem[];
+    float* a = smem;                                           // TR * ST
+    uint8_t* fl = reinterpret_cast<uint8_t*>(a + TR * ST);     // TR * ST
+    __shared__ int redbuf[64];
+    __shared__ float s_cm;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int bid = blockIdx.x;
+    const int bank = bid % NB; bid /= NB;
+    const int half = bid & 1;  bid >>= 1;
+    const int seg = bid % c.nseg;
+    const int frame = bid / c.nseg;
+    const uint16_t* rawf = raw + (size_t)frame * c.npix;
+    float* outf = out + (size_t)frame * c.npix;
+    const int mode = c.cm_mode;
+
+    // ---- load: raw + constants -> arrf in smem, keys in registers -------------------------------
+    uint32_t key[CPT * 8];
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+        const int ch = tid + j * NT;
+        const int r = ch / CH, cc = ch - r * CH;
+        const int gp = ((seg * ROWS + half * TR + r) * COLS) + bank * TC + cc * 8;
+        const uint4 rv = __ldcs(reinterpret_cast<const uint4*>(rawf + gp));
+        const uint2 fv = __ldg(reinterpret_cast<const uint2*>(c.flags + gp));
+        const uint32_t w[4] = {rv.x, rv.y, rv.z, rv.w};
+        float pa[8], pb[8], pc[8], oa[8], ob[8], oc[8];
+        if (DET == 0) {
+            ld8(c.ped0 + gp, pa);
+            ld8(c.ped1 + gp, pb);
+        } else {
+            ld8(c.peds + gp, pa);
+            ld8(c.peds + c.npix + gp, pb);
+            ld8(c.peds + 2 * (size_t)c.npix + gp, pc);
+            if (c.offs != nullptr) {
+                ld8(c.offs + gp, oa);
+                ld8(c.offs + c.npix + gp, ob);
+                ld8(c.offs + 2 * (size_t)c.npix + gp, oc);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t v = (i & 1) ? (w[i >> 1] >> 16) : (w[i >> 1] & 0xFFFFu);
+            const uint32_t f = (((i < 4 ? fv.x : fv.y) >> (8 * (i & 3))) & 0xFFu) | (c.ignore_keep ? PSR_FL_KEEP : 0u);
+            float x = (float)(v & 0x3FFFu);
+            uint32_t sel, elig;
+            if (DET == 0) {
+                sel = (v >> 14) & 1u;
+                x = __fsub_rn(x, sel ? pb[i] : pa[i]);
+                elig = sel ? (f & PSR_FL_ELIG1) : (f & PSR_FL_ELIG0);
+            } else {
+                const uint32_t gb = v >> 14;
+                sel = gb == 0 ? 0u : gb == 1 ? 1u : gb == 3 ? 2u : 3u;
+                float ped = 0.f, off = 0.f;
+                if (sel == 0) { ped = pa[i]; if (c.offs) off = oa[i]; }
+                else if (sel == 1) { ped = pb[i]; if (c.offs) off = ob[i]; }
+                else if (sel == 2) { ped = pc[i]; if (c.offs) off = oc[i]; }
+                x = __fsub_rn(x, ped);
+                if (c.offs != nullptr) x = __fsub_rn(x, off);
+                elig = (sel < 3 && ((c.elig_mask >> sel) & 1u) && (f & PSR_FL_MASK)) ? 1u : 0u;
+            }
+            const int si = r * ST + cc * 8 + i;
+            a[si] = x;
+            fl[si] = (uint8_t)((f & (PSR_FL_MASK | PSR_FL_KEEP)) | (elig ? 2u : 0u) | (sel << 4));
+            key[j * 8 + i] = elig ? psr_f2key(x) : KEY_INELIGIBLE;
+        }
+    }
+
+    // ---- mode 4: 2-d median over the whole tile (common_mode_2d: skip if n < npix_min, skip if |cm| > cormax)
+    if (mode & 4) {
+        BlockRed<NW> red{redbuf, 0};
+        int cnt = 0;
+#pragma unroll
+        for (int i = 0; i < CPT * 8; ++i) cnt += (key[i] != KEY_INELIGIBLE);
+        const int n = red.sum(cnt);
+        if (n >= c.npix_min && n > 0) {                    // uniform across the CTA
+            const int k1 = (n - 1) >> 1, k2 = n >> 1;
+            uint32_t prefix = 0;
+#pragma unroll 1
+            for (int bit = 31; bit >= 0; --bit) {
+                const uint32_t cand = prefix | (1u << bit);
+                int cl = 0;
+#pragma unroll
+                for (int i = 0; i < CPT * 8; ++i) cl += (key[i] < cand);
+                if (red.sum(cl) <= k1) prefix = cand;
+            }
+            const uint32_t lo = prefix;
+            uint32_t hi = lo;
+            if (k2 != k1) {
+                int cle = 0; uint32_t mg = 0xFFFFFFFFu;
+#pragma unroll
+                for (int i = 0; i < CPT * 8; ++i) { cle += (key[i] <= lo); if (key[i] > lo) mg = min(mg, key[i]); }
+                cle = red.sum(cle);
+                mg = red.minu(mg);
+                if (cle <= k2) hi = mg;
+            }
+            const float cm = psr_mid(psr_key2f(lo), psr_key2f(hi));
+            if (!(fabsf(cm) > c.cormax)) {
+#pragma unroll
+                for (int j = 0; j < CPT; ++j) {
+                    const int ch = tid + j * NT;
+                    const int r = ch / CH, cc = ch - r * CH;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        if (key[j * 8 + i] != KEY_INELIGIBLE) {
+                            const int si = r * ST + cc * 8 + i;
+                            a[si] = __fsub_rn(a[si], cm);
+                        }
+                }
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- mode 1: per-row medians within the bank (common_mode_rows: n > npix_min and |cm| < cormax)
+    if (mode & 1) {
+        constexpr int NK = (TC + 31) / 32;
+        for (int r = warp; r < TR; r += NW) {
+            uint32_t k[NK]; int cnt = 0;
+#pragma unroll
+            for (int i = 0; i < NK; ++i) {
+                const int col = lane + 32 * i;
+                k[i] = KEY_INELIGIBLE;
+                if (col < TC && (fl[r * ST + col] & 2u)) { k[i] = psr_f2key(a[r * ST + col]); ++cnt; }
+            }
+            const int n = __reduce_add_sync(0xFFFFFFFFu, cnt);
+            if (n > c.npix_min && n > 0) {
+                const float cm = warp_median<NK>(k, n);
+                if (fabsf(cm) < c.cormax) {
+#pragma unroll
+                    for (int i = 0; i < NK; ++i) {
+                        const int col = lane + 32 * i;
+                        if (k[i] != KEY_INELIGIBLE) a[r * ST + col] = __fsub_rn(a[r * ST + col], cm);
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+
+    // ---- mode 2: per-column medians within the half (common_mode_cols: same guards)
+    if (mode & 2) {
+        constexpr int NK = (TR + 31) / 32;
+        for (int col = warp; col < TC; col += NW) {
+            uint32_t k[NK]; int cnt = 0;
+#pragma unroll
+            for (int i = 0; i < NK; ++i) {
+                const int r = lane + 32 * i;
+                k[i] = KEY_INELIGIBLE;
+                if (r < TR && (fl[r * ST + col] & 2u)) { k[i] = psr_f2key(a[r * ST + col]); ++cnt; }
+            }
+            const int n = __reduce_add_sync(0xFFFFFFFFu, cnt);
+            if (n > c.npix_min && n > 0) {
+                const float cm = warp_median<NK>(k, n);
+                if (fabsf(cm) < c.cormax) {
+#pragma unroll
+                    for (int i = 0; i < NK; ++i) {
+                        const int r = lane + 32 * i;
+                        if (k[i] != KEY_INELIGIBLE) a[r * ST + col] = __fsub_rn(a[r * ST + col], cm);
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+    (void)s_cm;
+
+    // ---- epilogue: arrf * factor * mask, keep-select, stream out ---------------------------------
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+        const int ch = tid + j * NT;
+        const int r = ch / CH, cc = ch - r * CH;
+        const int gp = ((seg * ROWS + half * TR + r) * COLS) + bank * TC + cc * 8;
+        float ga[8], gb_[8], gc[8];
+        if (DET == 0) {
+            ld8(c.gf0 + gp, ga);
+            ld8(c.gf1 + gp, gb_);
+        } else {
+            ld8(c.gfac + gp, ga);
+            ld8(c.gfac + c.npix + gp, gb_);
+            ld8(c.gfac + 2 * (size_t)c.npix + gp, gc);
+        }
+        float o[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int si = r * ST + cc * 8 + i;
+            const uint32_t f = fl[si];
+            const uint32_t sel = f >> 4;
+            float gf;
+            if (DET == 0) gf = sel ? gb_[i] : ga[i];
+            else gf = sel == 0 ? ga[i] : sel == 1 ? gb_[i] : sel == 2 ? gc[i] : 1.0f;
+            const float v = __fmul_rn(__fmul_rn(a[si], gf), (f & PSR_FL_MASK) ? 1.0f : 0.0f);
+            o[i] = (f & PSR_FL_KEEP) ? v : 0.0f;
+        }
+        __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
+        __stcs(reinterpret_cast<float4*>(outf + gp + 4), make_float4(o[4], o[5], o[6], o[7]));
+    }
+}
+
+constexpr int EPIX_NT = 352, JF_NT = 512;
+constexpr size_t EPIX_SMEM = (size_t)(176 * 49) * 5;     // float + flag byte per padded tile pixel
+constexpr size_t JF_SMEM = (size_t)(256 * 65) * 5;
+
+}  // namespace
+
+cudaError_t psr_common_mode_setup(void)
+{
+    cudaError_t e = cudaFuncSetAttribute(cm_calib_kernel<0, 352, 384, 8, EPIX_NT>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_SMEM);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(cm_calib_kernel<1, 512, 1024, 16, JF_NT>,
+                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JF_SMEM);
+}
+
+cudaError_t psr_launch_common_mode(const PsrDev& c, const uint16_t* d_raw, int nframes, float* d_out, cudaStream_t st)
+{
+    if (nframes <= 0) return cudaSuccess;
+    if (c.det_kind == 0) {
+        const unsigned grid = (unsigned)nframes * c.nseg * 2 * 8;
+        cm_calib_kernel<0, 352, 384, 8, EPIX_NT><<<grid, EPIX_NT, EPIX_SMEM, st>>>(d_raw, d_out, c);
+    } else {
+        const unsigned grid = (unsigned)nframes * c.nseg * 2 * 16;
+        cm_calib_kernel<1, 512, 1024, 16, JF_NT><<<grid, JF_NT, JF_SMEM, st>>>(d_raw, d_out, c);
+    }
+    return cudaGetLastError();
+}
