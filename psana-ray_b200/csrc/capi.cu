@@ -74,7 +74,7 @@ struct psr_ctx {
     int32_t* d_inv = nullptr;
     uint8_t* d_keep_image = nullptr;
     float* d_scratch = nullptr; size_t scratch_elems = 0;
-    int frames_per_block = 16;
+    int frames_per_block = 0;      // 0 = auto: epix10ka 32 (constants L2-resident), jungfrau whole batch (151 MB of constants do not fit L2)
     HostPipe pipe;
 };
 
@@ -123,12 +123,13 @@ int ensure_scratch(psr_ctx* c, size_t elems) {
 
 int launch_batch(psr_ctx* c, const uint16_t* d_raw, int nframes, float* d_out, int out_kind, cudaStream_t st) {
     const PsrDev& d = c->dev;
+    const int fpb = c->frames_per_block > 0 ? c->frames_per_block : (d.det_kind == PSR_DET_EPIX10KA ? 32 : nframes);
     if (out_kind == PSR_OUT_CALIB) {
-        if (d.cm_mode == 0) PSR_CUDA(psr_launch_calib_map(d, d_raw, nframes, d_out, c->frames_per_block, st));
+        if (d.cm_mode == 0) PSR_CUDA(psr_launch_calib_map(d, d_raw, nframes, d_out, fpb, st));
         else                PSR_CUDA(psr_launch_common_mode(d, d_raw, nframes, d_out, st));
     } else {
         if (d.cm_mode == 0) {
-            PSR_CUDA(psr_launch_image_fused(d, d_raw, nframes, d_out, c->frames_per_block, st));
+            PSR_CUDA(psr_launch_image_fused(d, d_raw, nframes, d_out, fpb, st));
         } else {
             int rc = ensure_scratch(c, (size_t)nframes * d.npix);
             if (rc != PSR_OK) return rc;
