@@ -110,6 +110,29 @@ int psr_set_option(psr_ctx* ctx, const char* name, int value);
  *   d_out : PSR_OUT_CALIB (nframes, nseg, rows, cols) / PSR_OUT_IMAGE (nframes, H, W) float32 */
 int psr_calib_batch(psr_ctx* ctx, const uint16_t* d_raw, int nframes, float* d_out, int out_kind, void* stream);
 
+/* No counterpart in the reference: an image-mode hot call for callers that cannot allocate device
+ * memory.  Two kinds of caller are in that position: a monitoring or consumer process attached to a
+ * GPU whose memory another job (typically a PyTorch caching allocator) has already claimed, where
+ * cudaMalloc simply fails; and a latency-critical acquisition loop that must never take the
+ * device-wide synchronisation that cudaMalloc / cudaFree imply.  psr_calib_batch(PSR_OUT_IMAGE) with
+ * common mode on parks the calibrated frames in a scratch buffer the context allocates (psr_reserve
+ * or first use); this variant runs the same two kernels but parks them in a fixed array that is part
+ * of the library image, PSR_NOALLOC_SCRATCH_BYTES long, which every GPU that loads the library
+ * carries until the process exits.  It calls no cudaMalloc, cudaFree or any other allocating routine.
+ *   - limit: nframes * nseg*rows*cols * 4 bytes must fit the array -- 3 frames of epix10k2M, 1 frame
+ *     of Jungfrau 4M per call; larger requests are rejected with PSR_E_INVALID and a message naming
+ *     the limit.  Loop over the batch in slices.
+ *   - d_raw and d_img are the caller's, exactly as for psr_calib_batch; results are identical to it,
+ *     with common mode on or off.
+ *   - the first call on each device looks the array's device address up once (with that device
+ *     current); make that first call before starting any stream capture.
+ *   - the array is shared by every call and every context on the device and keeps the previous
+ *     call's contents; nothing in it has to start at zero, because each call overwrites the part it
+ *     later reads.  Two calls whose kernels overlap on the GPU (different streams, or different
+ *     host threads) race on it: keep calls on one device in one stream. */
+#define PSR_NOALLOC_SCRATCH_BYTES (32u << 20)
+int psr_calib_image_noalloc(psr_ctx* ctx, const uint16_t* d_raw, int nframes, float* d_img, void* stream);
+
 /* Gain-mode index per pixel (0..nmodes-1, 255 = no mode matches): the decode of
  * gain_maps_epix10ka_any / the jungfrau gain-bit ranges, exposed so it can be checked bit-exactly. */
 int psr_decode_gain_modes(psr_ctx* ctx, const uint16_t* d_raw, int nframes, uint8_t* d_modes, void* stream);

@@ -8,11 +8,21 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
 
+// Scratch of psr_calib_image_noalloc: lives in the library image, so no call ever allocates it.
+// Host code must not pass this name to a kernel -- on the host it is only a stand-in for the symbol;
+// the device address comes from cudaGetSymbolAddress, looked up once per device (see the entry point).
+static __device__ __align__(256) unsigned char g_noalloc_scratch[PSR_NOALLOC_SCRATCH_BYTES];
+
 namespace {
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+float* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
 
 thread_local std::string g_err;
 
@@ -359,6 +369,38 @@ int psr_calib_batch(psr_ctx* c, const uint16_t* d_raw, int nframes, float* d_out
     if (nframes == 0) return PSR_OK;
     DeviceGuard g(c->device);
     return launch_batch(c, d_raw, nframes, d_out, out_kind, static_cast<cudaStream_t>(stream));
+}
+
+int psr_calib_image_noalloc(psr_ctx* c, const uint16_t* d_raw, int nframes, float* d_img, void* stream) {
+    int rc = check_batch_args(c, d_raw, nframes, d_img, PSR_OUT_IMAGE);
+    if (rc != PSR_OK) return rc;
+    if (nframes == 0) return PSR_OK;
+    const size_t frame_bytes = (size_t)c->dev.npix * sizeof(float);
+    const size_t need = (size_t)nframes * frame_bytes;
+    if (need > (size_t)PSR_NOALLOC_SCRATCH_BYTES)
+        return fail(PSR_E_INVALID, "psr_calib_image_noalloc: %d frames need %zu bytes of scratch, the built-in array holds %u "
+                    "(at most %d frames of this detector per call); slice the batch", nframes, need,
+                    (unsigned)PSR_NOALLOC_SCRATCH_BYTES, (int)((size_t)PSR_NOALLOC_SCRATCH_BYTES / frame_bytes));
+    if (c->device < 0 || c->device >= NOALLOC_MAX_DEVICES) return fail(PSR_E_INVALID, "device index %d not supported here", c->device);
+    DeviceGuard g(c->device);
+    if (!g.ok) return fail(PSR_E_CUDA, "cudaSetDevice(%d) failed", c->device);
+    float* scratch = nullptr;
+    {   // once per device, with that device current: the symbol's address on THIS device
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_ptr[c->device]) {
+            void* p = nullptr;
+            PSR_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+            g_noalloc_ptr[c->device] = static_cast<float*>(p);
+        }
+        scratch = g_noalloc_ptr[c->device];
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    PsrDev t = c->dev; t.ignore_keep = 1;       // image mode: producer masks act on the 2-D image only
+    // pass 1 writes every pixel of frames [0, nframes) of the scratch, pass 2 reads exactly those: stale
+    // contents from an earlier call are never seen, so nothing is cleared
+    PSR_CUDA(psr_launch_common_mode(t, d_raw, nframes, scratch, st));
+    PSR_CUDA(psr_launch_image_gather(c->dev, scratch, nframes, d_img, st));
+    return PSR_OK;
 }
 
 int psr_decode_gain_modes(psr_ctx* c, const uint16_t* d_raw, int nframes, uint8_t* d_modes, void* stream) {

@@ -13,6 +13,7 @@ PSR_DET_EPIX10KA, PSR_DET_JUNGFRAU = 0, 1
 PSR_OUT_CALIB, PSR_OUT_IMAGE = 0, 1
 PSR_CM_ROWS, PSR_CM_COLS, PSR_CM_BANKS = 1, 2, 4
 PSR_IPC_HANDLE_BYTES = 64
+PSR_NOALLOC_SCRATCH_BYTES = 32 << 20
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libpsana_ray_cuda.so")
@@ -47,6 +48,7 @@ SIGNATURES = {
     "psr_reserve": (_i, [_vp, _i]),
     "psr_set_option": (_i, [_vp, C.c_char_p, _i]),
     "psr_calib_batch": (_i, [_vp, _vp, _i, _vp, _i, _vp]),
+    "psr_calib_image_noalloc": (_i, [_vp, _vp, _i, _vp, _vp]),
     "psr_decode_gain_modes": (_i, [_vp, _vp, _i, _vp, _vp]),
     "psr_calib_batch_host": (_i, [_vp, _vp, _i, _vp, _vp, _i]),
     "psr_set_host_chunk": (_i, [_vp, _i, _i]),

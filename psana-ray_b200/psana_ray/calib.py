@@ -117,6 +117,25 @@ class GpuCalibrator:
                                           N.PSR_OUT_IMAGE if image else N.PSR_OUT_CALIB, st))
         return out
 
+    def calib_image_noalloc(self, raw, out, stream=None):
+        """Image-mode calibration that allocates nothing on the device (psr_calib_image_noalloc).
+
+        For consumers that share a GPU whose memory is already spoken for, or loops that cannot afford
+        the device-wide stall of an allocation.  ``out`` must be supplied by the caller; at most
+        ``PSR_NOALLOC_SCRATCH_BYTES // (4 * npix)`` frames per call (3 for epix10k2M, 1 for Jungfrau 4M).
+        Calls on one device share one scratch array: keep them on one stream.
+        """
+        import torch
+        if raw.dtype not in (torch.uint16, torch.int16) or not raw.is_contiguous() or not raw.is_cuda:
+            raise ValueError("raw must be a contiguous uint16/int16 CUDA tensor")
+        nframes = raw.shape[0]
+        shape = self.out_shape(nframes, True)
+        if tuple(out.shape) != shape or out.dtype != torch.float32 or not out.is_contiguous():
+            raise ValueError(f"out must be a contiguous float32 CUDA tensor of shape {shape}")
+        st = stream if stream is not None else torch.cuda.current_stream(raw.device).cuda_stream
+        N.check(self._lib.psr_calib_image_noalloc(self._ctx, raw.data_ptr(), nframes, out.data_ptr(), st))
+        return out
+
     def calib_ptr(self, d_raw: int, nframes: int, d_out: int, image: bool = False, stream: int = 0):
         """Raw-pointer form of calib() for callers that manage their own device memory."""
         N.check(self._lib.psr_calib_batch(self._ctx, d_raw, nframes, d_out,
