@@ -19,6 +19,7 @@ namespace {
 
 constexpr int MAP_THREADS = 256;
 constexpr int MAP_UNROLL = 4;       // frames in flight per thread
+template <int N> struct IntC { static constexpr int value = N; };
 
 __device__ __forceinline__ float maskf(uint32_t flbyte) { return (flbyte & PSR_FL_MASK) ? 1.0f : 0.0f; }
 
@@ -35,10 +36,12 @@ template <bool HAS_OFFS>
 __device__ __forceinline__ float jf_px(uint32_t v, const float* p, const float* o, const float* g, uint32_t fl) {
     const uint32_t gb = v >> 14;                                 // 00 g0, 01 g1, 11 g2, 10 none
     float x = (float)(v & 0x3FFFu);
-    float ped = 0.0f, off = 0.0f, gf = 1.0f;
-    if (gb == 0)      { ped = p[0]; gf = g[0]; if (HAS_OFFS) off = o[0]; }
-    else if (gb == 1) { ped = p[1]; gf = g[1]; if (HAS_OFFS) off = o[1]; }
-    else if (gb == 3) { ped = p[2]; gf = g[2]; if (HAS_OFFS) off = o[2]; }
+    // branch-free select: the three candidates are already in registers
+    const bool is0 = gb == 0, is1 = gb == 1, is3 = gb == 3;
+    const float ped = is0 ? p[0] : is1 ? p[1] : is3 ? p[2] : 0.0f;
+    const float gf  = is0 ? g[0] : is1 ? g[1] : is3 ? g[2] : 1.0f;
+    float off = 0.0f;
+    if (HAS_OFFS) off = is0 ? o[0] : is1 ? o[1] : is3 ? o[2] : 0.0f;
     x = __fsub_rn(x, ped);                                       // arrf[gr] -= peds[i][gr]   (x - 0 is exact)
     if (HAS_OFFS) x = __fsub_rn(x, off);                         // arrf -= offset, separately rounded
     float r = __fmul_rn(__fmul_rn(x, gf), maskf(fl));
@@ -51,7 +54,7 @@ __device__ __forceinline__ float f4get(const float4& v, int i) { return i == 0 ?
 // K1: epix10ka calib map.  A warp covers 64 groups of 4 pixels; lane L owns groups L and L+32 so
 // that both the 8-byte raw loads and the 16-byte output stores of a warp instruction are contiguous.
 // =================================================================================================
-__global__ void __launch_bounds__(MAP_THREADS)
+__global__ void __launch_bounds__(MAP_THREADS, 3)
 epix_calib_map_kernel(const uint2* __restrict__ raw, float4* __restrict__ out,
                       const float4* __restrict__ ped0, const float4* __restrict__ gf0,
                       const float4* __restrict__ ped1, const float4* __restrict__ gf1,
@@ -71,34 +74,34 @@ epix_calib_map_kernel(const uint2* __restrict__ raw, float4* __restrict__ out,
     else     { p0[1] = p0[0]; q0[1] = q0[0]; p1[1] = p1[0]; q1[1] = q1[0]; fl[1] = fl[0]; }
     const int gi[2] = {g0i, ok1 ? g1i : g0i};
 
-    for (int f = f_begin; f < f_end; f += MAP_UNROLL) {
-        uint2 r[MAP_UNROLL][2];
+    auto frames = [&](int f, auto nconst) {           // nconst frames starting at f, loads first, then math + stores
+        constexpr int NF = decltype(nconst)::value;
+        uint2 r[NF][2];
 #pragma unroll
-        for (int u = 0; u < MAP_UNROLL; ++u) {
-            if (f + u < f_end) {
-                const size_t base = (size_t)(f + u) * ngroups;
-                r[u][0] = __ldcs(raw + base + gi[0]);
-                r[u][1] = __ldcs(raw + base + gi[1]);
-            }
+        for (int u = 0; u < NF; ++u) {
+            const size_t base = (size_t)(f + u) * ngroups;
+            r[u][0] = __ldcs(raw + base + gi[0]);
+            r[u][1] = __ldcs(raw + base + gi[1]);
         }
 #pragma unroll
-        for (int u = 0; u < MAP_UNROLL; ++u) {
-            if (f + u < f_end) {
-                const size_t base = (size_t)(f + u) * ngroups;
+        for (int u = 0; u < NF; ++u) {
+            const size_t base = (size_t)(f + u) * ngroups;
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    if (h == 1 && !ok1) break;
-                    const uint32_t a = r[u][h].x, b = r[u][h].y;
-                    float4 o;
-                    o.x = epix_px(a & 0xFFFFu, p0[h].x, q0[h].x, p1[h].x, q1[h].x, fl[h]);
-                    o.y = epix_px(a >> 16,     p0[h].y, q0[h].y, p1[h].y, q1[h].y, fl[h] >> 8);
-                    o.z = epix_px(b & 0xFFFFu, p0[h].z, q0[h].z, p1[h].z, q1[h].z, fl[h] >> 16);
-                    o.w = epix_px(b >> 16,     p0[h].w, q0[h].w, p1[h].w, q1[h].w, fl[h] >> 24);
-                    __stcs(out + base + gi[h], o);
-                }
+            for (int h = 0; h < 2; ++h) {
+                if (h == 1 && !ok1) break;
+                const uint32_t a = r[u][h].x, b = r[u][h].y;
+                float4 o;
+                o.x = epix_px(a & 0xFFFFu, p0[h].x, q0[h].x, p1[h].x, q1[h].x, fl[h]);
+                o.y = epix_px(a >> 16,     p0[h].y, q0[h].y, p1[h].y, q1[h].y, fl[h] >> 8);
+                o.z = epix_px(b & 0xFFFFu, p0[h].z, q0[h].z, p1[h].z, q1[h].z, fl[h] >> 16);
+                o.w = epix_px(b >> 16,     p0[h].w, q0[h].w, p1[h].w, q1[h].w, fl[h] >> 24);
+                __stcs(out + base + gi[h], o);
             }
         }
-    }
+    };
+    int f = f_begin;
+    for (; f + MAP_UNROLL <= f_end; f += MAP_UNROLL) frames(f, IntC<MAP_UNROLL>{});
+    for (; f < f_end; ++f) frames(f, IntC<1>{});
 }
 
 // =================================================================================================
@@ -126,23 +129,24 @@ jf_calib_map_kernel(const uint2* __restrict__ raw, float4* __restrict__ out,
     }
     const uint32_t fl = __ldg(flags + g);
 
-    for (int f = f_begin; f < f_end; f += MAP_UNROLL) {
-        uint2 r[MAP_UNROLL];
+    auto frames = [&](int f, auto nconst) {
+        constexpr int NF = decltype(nconst)::value;
+        uint2 r[NF];
 #pragma unroll
-        for (int u = 0; u < MAP_UNROLL; ++u)
-            if (f + u < f_end) r[u] = __ldcs(raw + (size_t)(f + u) * ngroups + g);
+        for (int u = 0; u < NF; ++u) r[u] = __ldcs(raw + (size_t)(f + u) * ngroups + g);
 #pragma unroll
-        for (int u = 0; u < MAP_UNROLL; ++u) {
-            if (f + u < f_end) {
-                float4 o;
-                o.x = jf_px<HAS_OFFS>(r[u].x & 0xFFFFu, P[0], O[0], G[0], fl);
-                o.y = jf_px<HAS_OFFS>(r[u].x >> 16,     P[1], O[1], G[1], fl >> 8);
-                o.z = jf_px<HAS_OFFS>(r[u].y & 0xFFFFu, P[2], O[2], G[2], fl >> 16);
-                o.w = jf_px<HAS_OFFS>(r[u].y >> 16,     P[3], O[3], G[3], fl >> 24);
-                __stcs(out + (size_t)(f + u) * ngroups + g, o);
-            }
+        for (int u = 0; u < NF; ++u) {
+            float4 o;
+            o.x = jf_px<HAS_OFFS>(r[u].x & 0xFFFFu, P[0], O[0], G[0], fl);
+            o.y = jf_px<HAS_OFFS>(r[u].x >> 16,     P[1], O[1], G[1], fl >> 8);
+            o.z = jf_px<HAS_OFFS>(r[u].y & 0xFFFFu, P[2], O[2], G[2], fl >> 16);
+            o.w = jf_px<HAS_OFFS>(r[u].y >> 16,     P[3], O[3], G[3], fl >> 24);
+            __stcs(out + (size_t)(f + u) * ngroups + g, o);
         }
-    }
+    };
+    int f = f_begin;
+    for (; f + MAP_UNROLL <= f_end; f += MAP_UNROLL) frames(f, IntC<MAP_UNROLL>{});
+    for (; f < f_end; ++f) frames(f, IntC<1>{});
 }
 
 // =================================================================================================

@@ -86,6 +86,68 @@ __device__ __forceinline__ float warp_median(const uint32_t (&key)[NK], int n) {
     return psr_mid(psr_key2f(lo), psr_key2f(hi));
 }
 
+// ---- CTA-wide exact selection: 3-pass radix select (11 + 11 + 10 bits) on a 2048-bin shared histogram.
+// Keys stay in registers; bit i of `elig` says key[i] takes part.  Returns the k-th smallest (0-based)
+// eligible key; k must be < the number of eligible keys.  Every thread of the CTA must call it.
+// hist: 2048 words of shared memory; sh: 34 ints of shared memory.
+template <int NT, int NKEY, int PASS>
+__device__ __forceinline__ void block_kth_pass(const uint32_t (&key)[NKEY], uint32_t elig, uint32_t& prefix, int& k,
+                                               uint32_t* hist, int* sh)
+{
+    constexpr int NB = 2048, BPT = (NB + NT - 1) / NT, NW = NT / 32;
+    constexpr int SHIFT = PASS == 0 ? 21 : PASS == 1 ? 10 : 0;          // digit position
+    constexpr int HSHIFT = PASS == 1 ? 21 : 10;                         // bits above the digit (PASS > 0)
+    constexpr uint32_t DMASK = PASS == 2 ? 0x3FFu : 0x7FFu;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+    for (int i = 0; i < NKEY; ++i) {
+        bool m = (elig >> i) & 1u;
+        if (PASS > 0) m = m && ((key[i] >> HSHIFT) == prefix);
+        if (m) atomicAdd(&hist[(key[i] >> SHIFT) & DMASK], 1u);
+    }
+    __syncthreads();
+    uint32_t b[BPT]; uint32_t s = 0;
+#pragma unroll
+    for (int j = 0; j < BPT; ++j) {
+        const int idx = tid * BPT + j;
+        b[j] = idx < NB ? hist[idx] : 0u;
+        if (idx < NB) hist[idx] = 0u;                // owner re-zeroes its bins for the next pass
+        s += b[j];
+    }
+    uint32_t incl = s;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+    if (lane == 31) sh[warp] = (int)incl;
+    __syncthreads();
+    uint32_t base = 0;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) base += (w < warp) ? (uint32_t)sh[w] : 0u;
+    const uint32_t excl = base + incl - s;
+    if ((uint32_t)k >= excl && (uint32_t)k < excl + s) {
+        uint32_t r = (uint32_t)k - excl; int bin = tid * BPT; bool done = false;
+#pragma unroll
+        for (int j = 0; j < BPT; ++j) {
+            if (!done) { if (r < b[j]) { bin = tid * BPT + j; done = true; } else r -= b[j]; }
+        }
+        sh[32] = bin; sh[33] = (int)r;
+    }
+    __syncthreads();
+    prefix = (prefix << (PASS == 2 ? 10 : 11)) | (uint32_t)sh[32];
+    k = sh[33];
+}
+
+template <int NT, int NKEY>
+__device__ __forceinline__ uint32_t block_kth(const uint32_t (&key)[NKEY], uint32_t elig, int k, uint32_t* hist, int* sh)
+{
+    for (int i = threadIdx.x; i < 2048; i += NT) hist[i] = 0u;
+    __syncthreads();
+    uint32_t prefix = 0;
+    block_kth_pass<NT, NKEY, 0>(key, elig, prefix, k, hist, sh);
+    block_kth_pass<NT, NKEY, 1>(key, elig, prefix, k, hist, sh);
+    block_kth_pass<NT, NKEY, 2>(key, elig, prefix, k, hist, sh);
+    return prefix;
+}
+
 // smem flag byte of a tile pixel: bit0 mask, bit1 eligible (this frame), bit3 keep, bits 4-5 gain selector
 //   epix10ka selector: data bit 14;  jungfrau selector: 0,1,2 = g0,g1,g2, 3 = none
 template <int DET, int ROWS, int COLS, int NB, int NT>
@@ -100,7 +162,8 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     float* a = smem;                                           // TR * ST
     uint8_t* fl = reinterpret_cast<uint8_t*>(a + TR * ST);     // TR * ST
     __shared__ int redbuf[64];
-    __shared__ float s_cm;
+    __shared__ uint32_t hist[2048];
+    __shared__ int selsh[34];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int bid = blockIdx.x;
@@ -173,15 +236,10 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
         const int n = red.sum(cnt);
         if (n >= c.npix_min && n > 0) {                    // uniform across the CTA
             const int k1 = (n - 1) >> 1, k2 = n >> 1;
-            uint32_t prefix = 0;
-#pragma unroll 1
-            for (int bit = 31; bit >= 0; --bit) {
-                const uint32_t cand = prefix | (1u << bit);
-                int cl = 0;
+            uint32_t elig = 0;
 #pragma unroll
-                for (int i = 0; i < CPT * 8; ++i) cl += (key[i] < cand);
-                if (red.sum(cl) <= k1) prefix = cand;
-            }
+            for (int i = 0; i < CPT * 8; ++i) elig |= (key[i] != KEY_INELIGIBLE ? 1u : 0u) << i;
+            const uint32_t prefix = block_kth<NT, CPT * 8>(key, elig, k1, hist, selsh);
             const uint32_t lo = prefix;
             uint32_t hi = lo;
             if (k2 != k1) {
@@ -261,7 +319,6 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
         }
         __syncthreads();
     }
-    (void)s_cm;
 
     // ---- epilogue: arrf * factor * mask, keep-select, stream out ---------------------------------
 #pragma unroll
@@ -295,6 +352,125 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     }
 }
 
+
+// =================================================================================================
+// mode 4 only (the per-bank 2-d median -- the usual setting): no shared-memory tile at all.  Each
+// thread keeps the keys of its CPT*8 pixels in registers from load to store; eligibility, gain
+// selector, mask and keep bits are packed in four 32-bit registers.
+// =================================================================================================
+template <int DET, int ROWS, int COLS, int NB, int NT, int MINB>
+__global__ void __launch_bounds__(NT, MINB)
+cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c)
+{
+    constexpr int TR = ROWS / 2, TC = COLS / NB, CH = TC / 8, NCH = TR * CH, CPT = NCH / NT, NK = CPT * 8;
+    constexpr int NW = NT / 32;
+    static_assert(NCH % NT == 0 && NT % 32 == 0 && NK <= 32, "tile must split evenly over the CTA");
+    __shared__ int redbuf[64];
+    __shared__ uint32_t hist[2048];
+    __shared__ int selsh[34];
+
+    const int tid = threadIdx.x;
+    int bid = blockIdx.x;
+    const int bank = bid % NB; bid /= NB;
+    const int half = bid & 1;  bid >>= 1;
+    const int seg = bid % c.nseg;
+    const int frame = bid / c.nseg;
+    const uint16_t* rawf = raw + (size_t)frame * c.npix;
+    float* outf = out + (size_t)frame * c.npix;
+
+    uint32_t key[NK];
+    uint32_t elig = 0, sel0 = 0, sel1 = 0, mbits = 0, kbits = 0;
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+        const int ch = tid + j * NT;
+        const int r = ch / CH, cc = ch - r * CH;
+        const int gp = ((seg * ROWS + half * TR + r) * COLS) + bank * TC + cc * 8;
+        const uint4 rv = __ldcs(reinterpret_cast<const uint4*>(rawf + gp));
+        const uint2 fv = __ldg(reinterpret_cast<const uint2*>(c.flags + gp));
+        const uint32_t w[4] = {rv.x, rv.y, rv.z, rv.w};
+        float pa[8], pb[8], pc[8], oa[8], ob[8], oc[8];
+        if (DET == 0) { ld8(c.ped0 + gp, pa); ld8(c.ped1 + gp, pb); }
+        else {
+            ld8(c.peds + gp, pa); ld8(c.peds + c.npix + gp, pb); ld8(c.peds + 2 * (size_t)c.npix + gp, pc);
+            if (c.offs != nullptr) { ld8(c.offs + gp, oa); ld8(c.offs + c.npix + gp, ob); ld8(c.offs + 2 * (size_t)c.npix + gp, oc); }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int q = j * 8 + i;
+            const uint32_t v = (i & 1) ? (w[i >> 1] >> 16) : (w[i >> 1] & 0xFFFFu);
+            const uint32_t f = (((i < 4 ? fv.x : fv.y) >> (8 * (i & 3))) & 0xFFu) | (c.ignore_keep ? PSR_FL_KEEP : 0u);
+            float x = (float)(v & 0x3FFFu);
+            uint32_t sel, el;
+            if (DET == 0) {
+                sel = (v >> 14) & 1u;
+                x = __fsub_rn(x, sel ? pb[i] : pa[i]);
+                el = sel ? (f & PSR_FL_ELIG1) : (f & PSR_FL_ELIG0);
+            } else {
+                const uint32_t gb = v >> 14;
+                sel = gb == 0 ? 0u : gb == 1 ? 1u : gb == 3 ? 2u : 3u;
+                float ped = 0.f, off = 0.f;
+                if (sel == 0) { ped = pa[i]; if (c.offs) off = oa[i]; }
+                else if (sel == 1) { ped = pb[i]; if (c.offs) off = ob[i]; }
+                else if (sel == 2) { ped = pc[i]; if (c.offs) off = oc[i]; }
+                x = __fsub_rn(x, ped);
+                if (c.offs != nullptr) x = __fsub_rn(x, off);
+                el = (sel < 3 && ((c.elig_mask >> sel) & 1u) && (f & PSR_FL_MASK)) ? 1u : 0u;
+            }
+            key[q] = psr_f2key(x);
+            elig |= (el ? 1u : 0u) << q;
+            sel0 |= (sel & 1u) << q; sel1 |= (sel >> 1) << q;
+            mbits |= (f & PSR_FL_MASK ? 1u : 0u) << q;
+            kbits |= (f & PSR_FL_KEEP ? 1u : 0u) << q;
+        }
+    }
+
+    // common_mode_2d: skip if n < npix_min, skip if |cm| > cormax
+    BlockRed<NW> red{redbuf, 0};
+    const int n = red.sum(__popc(elig));
+    float cm = 0.f; bool apply = false;
+    if (n >= c.npix_min && n > 0) {                        // uniform across the CTA
+        const int k1 = (n - 1) >> 1, k2 = n >> 1;
+        const uint32_t lo = block_kth<NT, NK>(key, elig, k1, hist, selsh);
+        uint32_t hi = lo;
+        if (k2 != k1) {
+            int cle = 0; uint32_t mg = 0xFFFFFFFFu;
+#pragma unroll
+            for (int i = 0; i < NK; ++i)
+                if ((elig >> i) & 1u) { cle += (key[i] <= lo); if (key[i] > lo) mg = min(mg, key[i]); }
+            cle = red.sum(cle);
+            mg = red.minu(mg);
+            if (cle <= k2) hi = mg;
+        }
+        cm = psr_mid(psr_key2f(lo), psr_key2f(hi));
+        apply = !(fabsf(cm) > c.cormax);
+    }
+
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+        const int ch = tid + j * NT;
+        const int r = ch / CH, cc = ch - r * CH;
+        const int gp = ((seg * ROWS + half * TR + r) * COLS) + bank * TC + cc * 8;
+        float ga[8], gb_[8], gc[8];
+        if (DET == 0) { ld8(c.gf0 + gp, ga); ld8(c.gf1 + gp, gb_); }
+        else { ld8(c.gfac + gp, ga); ld8(c.gfac + c.npix + gp, gb_); ld8(c.gfac + 2 * (size_t)c.npix + gp, gc); }
+        float o[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int q = j * 8 + i;
+            float x = psr_key2f(key[q]);
+            if (apply && ((elig >> q) & 1u)) x = __fsub_rn(x, cm);
+            const uint32_t sel = ((sel0 >> q) & 1u) | (((sel1 >> q) & 1u) << 1);
+            float gf;
+            if (DET == 0) gf = sel ? gb_[i] : ga[i];
+            else gf = sel == 0 ? ga[i] : sel == 1 ? gb_[i] : sel == 2 ? gc[i] : 1.0f;
+            const float v = __fmul_rn(__fmul_rn(x, gf), ((mbits >> q) & 1u) ? 1.0f : 0.0f);
+            o[i] = ((kbits >> q) & 1u) ? v : 0.0f;
+        }
+        __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
+        __stcs(reinterpret_cast<float4*>(outf + gp + 4), make_float4(o[4], o[5], o[6], o[7]));
+    }
+}
+
 constexpr int EPIX_NT = 352, JF_NT = 512;
 constexpr size_t EPIX_SMEM = (size_t)(176 * 49) * 5;     // float + flag byte per padded tile pixel
 constexpr size_t JF_SMEM = (size_t)(256 * 65) * 5;
@@ -315,10 +491,12 @@ cudaError_t psr_launch_common_mode(const PsrDev& c, const uint16_t* d_raw, int n
     if (nframes <= 0) return cudaSuccess;
     if (c.det_kind == 0) {
         const unsigned grid = (unsigned)nframes * c.nseg * 2 * 8;
-        cm_calib_kernel<0, 352, 384, 8, EPIX_NT><<<grid, EPIX_NT, EPIX_SMEM, st>>>(d_raw, d_out, c);
+        if (c.cm_mode == 4) cm_banks_kernel<0, 352, 384, 8, EPIX_NT, 2><<<grid, EPIX_NT, 0, st>>>(d_raw, d_out, c);
+        else cm_calib_kernel<0, 352, 384, 8, EPIX_NT><<<grid, EPIX_NT, EPIX_SMEM, st>>>(d_raw, d_out, c);
     } else {
         const unsigned grid = (unsigned)nframes * c.nseg * 2 * 16;
-        cm_calib_kernel<1, 512, 1024, 16, JF_NT><<<grid, JF_NT, JF_SMEM, st>>>(d_raw, d_out, c);
+        if (c.cm_mode == 4) cm_banks_kernel<1, 512, 1024, 16, JF_NT, 1><<<grid, JF_NT, 0, st>>>(d_raw, d_out, c);
+        else cm_calib_kernel<1, 512, 1024, 16, JF_NT><<<grid, JF_NT, JF_SMEM, st>>>(d_raw, d_out, c);
     }
     return cudaGetLastError();
 }

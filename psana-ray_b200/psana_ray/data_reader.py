@@ -1,0 +1,154 @@
+"""DataReader -- the consumer handle of the reference, same methods, GPU-resident payload.
+
+Reference: ``psana_ray/data_reader.py`` -- ctor defaults ``address='auto', queue_name="shared_queue",
+ray_namespace='my'`` (:5); ``connect()`` (:11-24); ``read()`` returns one item or ``None`` (:31-35),
+raises ``RuntimeError`` when unconnected (:32-33) and ``DataReaderError`` when the queue is dead
+(:36-37); ``close()`` (:26-29); context manager (:39-44); ``DataReaderError`` (:46-48).
+
+An item is still the reference's ``[rank, idx, data, photon_energy]`` (ref: producer.py:101);
+``data`` is now a CUDA ``torch.Tensor`` view -- ``(segs, rows, cols)`` or ``(1, H, W)`` float32 --
+into the producer's slab, mapped once per slab through CUDA IPC, instead of an ndarray unpickled
+from the object store.  Producers queue whole batches; ``read()`` de-batches locally, so most calls
+cost no round trip at all.  Additive: ``read_batch()``, ``__iter__`` (stops at the end-of-stream
+sentinel, which ``read()`` cannot tell from an empty queue -- both are ``None`` in the reference).
+"""
+import time
+
+from .shared_queue import QueueDeadError, get_queue
+from .transport import EventBatch, GpuBatchRef
+
+
+class DataReader:
+    def __init__(self, address='auto', queue_name="shared_queue", ray_namespace='my', device=None):
+        self.address = address
+        self.queue_name = queue_name
+        self.ray_namespace = ray_namespace
+        self.device = device          # CUDA device GPU batches are mapped on; None = current device at first use
+        self._queue = None
+        self._mapper = None
+        self._batch = None            # EventBatch being handed out
+        self._tensor = None           # its data, mapped
+        self._cursor = 0
+        self.end_of_stream = False
+
+    # -- reference surface --------------------------------------------------------------------------------
+    def connect(self):
+        try:
+            self._queue = get_queue(self.queue_name, self.ray_namespace, self.address)
+        except Exception as e:
+            print(f"Error getting queue actor: {e}")
+            self.close()
+            raise
+
+    def close(self):
+        self._finish_batch()
+        if self._queue is not None:
+            self._queue.close()
+        self._queue = None
+        if self._mapper is not None:
+            self._mapper.close()
+            self._mapper = None
+
+    def read(self):
+        """One ``[rank, idx, data, photon_energy]``, or ``None`` when nothing is available."""
+        found, item = self._read_ex()
+        return item if found else None
+
+    def __enter__(self):
+        self.connect()
+        return self
+
+    def __exit__(self, exc_type, exc_val, exc_tb):
+        self.close()
+
+    # -- additive -------------------------------------------------------------------------------------------
+    def read_batch(self):
+        """The rest of the current batch (or the next one) as ``[rank, idx0, data(n, ...), photon_energies]``; None if empty."""
+        if self._queue is None:
+            raise RuntimeError("DataReader is not connected. Call connect() first.")
+        if self._batch is None and not self._fetch():
+            return None
+        if self._batch is None:
+            return None
+        b, c = self._batch, self._cursor
+        out = [b.rank, b.idx0 + c, self._tensor[c:], list(b.photon_energy[c:])]
+        self._cursor = b.count
+        return out
+
+    def __iter__(self):
+        """Yields items until the producer's end-of-stream sentinel; polls while the queue is merely empty."""
+        while True:
+            found, item = self._read_ex()
+            if found and item is None:
+                return
+            if not found:
+                time.sleep(0.001)
+                continue
+            yield item
+
+    # -- internals --------------------------------------------------------------------------------------------
+    def _finish_batch(self):
+        b = self._batch
+        self._batch = self._tensor = None
+        self._cursor = 0
+        if b is not None and b.lease is not None and self._queue is not None:
+            try:
+                self._queue.release(b.lease)
+            except Exception:
+                pass
+
+    def _map(self, data):
+        if isinstance(data, GpuBatchRef):
+            if self._mapper is None:
+                import torch
+                from .transport import SlabMapper
+                dev = self.device if self.device is not None else torch.cuda.current_device()
+                self._mapper = SlabMapper(dev)
+            return self._mapper.map(data)
+        return data
+
+    def _fetch(self):
+        """Pull the next queue item.  Returns False if the queue was empty; sets end_of_stream on a sentinel."""
+        try:
+            found, item = self._queue.get_ex()
+        except QueueDeadError as e:
+            raise DataReaderError("Queue actor is dead.") from e
+        if not found:
+            return False
+        if item is None:
+            self.end_of_stream = True
+            self._pending_sentinel = True
+            return True
+        if isinstance(item, EventBatch):
+            self._batch, self._cursor = item, 0
+            self._tensor = self._map(item.data)
+        else:
+            self._loose = item            # a plain item put by some other client: hand it through untouched
+        return True
+
+    _pending_sentinel = False
+    _loose = None
+
+    def _read_ex(self):
+        """(found, item): found=False means the queue was empty; (True, None) is the end-of-stream sentinel."""
+        if self._queue is None:
+            raise RuntimeError("DataReader is not connected. Call connect() first.")
+        if self._batch is not None and self._cursor >= self._batch.count:
+            self._finish_batch()
+        if self._batch is None:
+            if not self._fetch():
+                return False, None
+            if self._pending_sentinel:
+                self._pending_sentinel = False
+                return True, None
+            if self._loose is not None:
+                item, self._loose = self._loose, None
+                return True, item
+        b, c = self._batch, self._cursor
+        self._cursor += 1
+        return True, [b.rank, b.idx0 + c, self._tensor[c], b.photon_energy[c]]
+
+
+class DataReaderError(Exception):
+    """Custom exception for DataReader errors."""
+    pass

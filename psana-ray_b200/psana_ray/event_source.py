@@ -1,0 +1,131 @@
+"""Event sources with the shape of ``psana_wrapper.PsanaWrapperSmd`` as the reference uses it.
+
+Reference call sites (the class itself is third-party, [EXT]): constructed with ``exp=, run=,
+detector_name=`` (ref: psana_ray/producer.py:150-154), ``create_bad_pixel_mask()`` (:81),
+``iter_events(mode=)`` yielding ``(data, photon_energy)`` (:88), modes ``ImageRetrievalMode.calib /
+.image`` (:156-159).  Events are sharded round-robin over MPI ranks by psana's ``MPIDataSource``:
+rank r sees the events with ``nevent % size == r``.
+
+The GPU path moves calibration out of the source: a source here yields RAW uint16 frames
+(``iter_raw_events``) and exposes the per-run constants once (``constants()``, ``geometry()``), and
+the producer calibrates whole batches on its GPU.
+
+  * ``SyntheticSource`` -- seeded frames of the named detector shape (psana and the LCLS file
+    system are not available offline); used by the CLI by default, by the tests and by bench.py.
+  * ``PsanaSource`` -- the same interface over a real psana ``MPIDataSource`` + ``Detector``; only
+    importable where psana is installed; untested here.
+"""
+from __future__ import annotations
+
+import enum
+import zlib
+
+import numpy as np
+
+from . import synthetic as syn
+
+
+class ImageRetrievalMode(enum.Enum):
+    raw = 0
+    calib = 1
+    image = 2
+
+
+class SyntheticSource:
+    def __init__(self, exp, run, detector_name, rank=0, size=1, num_events=256, pool=8, cfg_variant="aml",
+                 common_mode=None, nseg=None):
+        self.exp, self.run, self.detector_name = exp, int(run), detector_name
+        self.rank, self.size = int(rank), int(size)
+        self.num_events = int(num_events)
+        self.spec = syn.detector_spec(detector_name)
+        if nseg is not None:
+            self.spec = self.spec.with_nseg(nseg)
+        self.seed = zlib.crc32(f"{exp}:{self.run}:{detector_name}".encode()) & 0x7FFFFFFF
+        self._consts = syn.make_constants(self.spec, seed=self.seed, cfg_variant=cfg_variant)
+        self._cmpars = common_mode
+        self._pool = syn.make_raw_frames(self.spec, self._consts, pool, seed=self.seed + 1)
+        self._geo = None
+
+    # -- per-run constants (psana: det.pedestals / gain / offset / mask / common_mode / indexes_x,y) ------
+    def constants(self):
+        return self._consts
+
+    def common_mode(self):
+        return self._cmpars
+
+    def geometry(self):
+        if self._geo is None:
+            self._geo = syn.make_pixel_index_arrays(self.spec)
+        return self._geo
+
+    def create_bad_pixel_mask(self):
+        """det.mask(run, calib=True, status=True, edges=True, central=True, unbond=True, unbondnbrs=True): 1 = good."""
+        return self._consts["mask"]
+
+    # -- events -----------------------------------------------------------------------------------------------
+    def raw_event(self, nevent):
+        """Deterministic raw frame of global event number ``nevent`` (any rank computes the same bytes)."""
+        base = self._pool[nevent % self._pool.shape[0]]
+        twist = np.uint16((nevent * 2654435761 >> 7) & 0x01FF)       # perturbs ADC bits only, keeps the gain bits
+        return base ^ twist
+
+    def photon_energy(self, nevent):
+        return 9500.0 + 0.25 * (nevent % 400)
+
+    def iter_raw_events(self):
+        for n in range(self.rank, self.num_events, self.size):          # nevent % size == rank
+            yield self.raw_event(n), self.photon_energy(n)
+
+    def event_numbers(self):
+        return list(range(self.rank, self.num_events, self.size))
+
+
+class PsanaSource:
+    """psana-backed source (LCLS-I psana1).  Needs ``import psana``; raises ImportError otherwise."""
+
+    def __init__(self, exp, run, detector_name, rank=0, size=1, epix10ka_cfg=None):
+        import psana                                                      # noqa: F401  (not available offline)
+        self._psana = psana
+        self.exp, self.run, self.detector_name = exp, int(run), detector_name
+        self.rank, self.size = rank, size
+        self.ds = psana.MPIDataSource(f"exp={exp}:run={self.run}:smd")
+        self.det = psana.Detector(detector_name)
+        self.ebeam = psana.Detector("EBeam")
+        self.spec = syn.detector_spec(detector_name)
+        self._cfg = epix10ka_cfg
+
+    def constants(self):
+        r = self.run
+        out = {"peds": np.asarray(self.det.pedestals(r), dtype=np.float32),
+               "gain": np.asarray(self.det.gain(r), dtype=np.float32),
+               "mask": np.asarray(self.create_bad_pixel_mask(), dtype=np.uint8)}
+        if self.spec.kind == "jungfrau":
+            offs = self.det.offset(r)
+            if offs is not None:
+                out["offs"] = np.asarray(offs, dtype=np.float32)
+        else:
+            if self._cfg is None:
+                raise RuntimeError("epix10ka needs the per-pixel config bytes (pixel gain bits | trbit << 4); "
+                                   "pass epix10ka_cfg built from the detector's configuration object")
+            out["cfg"] = np.asarray(self._cfg, dtype=np.uint8)
+        self.spec = self.spec.with_nseg(out["peds"].shape[1])
+        return out
+
+    def common_mode(self):
+        cm = self.det.common_mode(self.run)
+        return None if cm is None else tuple(cm)
+
+    def geometry(self):
+        return (np.asarray(self.det.indexes_x(self.run), dtype=np.int32),
+                np.asarray(self.det.indexes_y(self.run), dtype=np.int32))
+
+    def create_bad_pixel_mask(self):
+        return self.det.mask(self.run, calib=True, status=True, edges=True, central=True, unbond=True, unbondnbrs=True)
+
+    def iter_raw_events(self):
+        for evt in self.ds.events():                                      # MPIDataSource shards nevent % size == rank
+            raw = self.det.raw(evt)
+            if raw is None:
+                continue
+            eb = self.ebeam.get(evt)
+            yield np.asarray(raw, dtype=np.uint16), (eb.ebeamPhotonEnergy() if eb is not None else None)
