@@ -31,17 +31,25 @@ __device__ __forceinline__ float epix_px(uint32_t v, float p0, float g0, float p
     return (fl & PSR_FL_KEEP) ? o : 0.0f;
 }
 
+// a if p != 0 else b, as one SELP
+__device__ __forceinline__ float selp(float a, float b, uint32_t p) {
+    float r;
+    asm("{ .reg .pred q; setp.ne.u32 q, %3, 0; selp.f32 %0, %1, %2, q; }" : "=f"(r) : "f"(a), "f"(b), "r"(p));
+    return r;
+}
+
 // ---- one jungfrau pixel -------------------------------------------------------------------------
 template <bool HAS_OFFS>
 __device__ __forceinline__ float jf_px(uint32_t v, const float* p, const float* o, const float* g, uint32_t fl) {
     const uint32_t gb = v >> 14;                                 // 00 g0, 01 g1, 11 g2, 10 none
     float x = (float)(v & 0x3FFFu);
-    // branch-free select: the three candidates are already in registers
-    const bool is0 = gb == 0, is1 = gb == 1, is3 = gb == 3;
-    const float ped = is0 ? p[0] : is1 ? p[1] : is3 ? p[2] : 0.0f;
-    const float gf  = is0 ? g[0] : is1 ? g[1] : is3 ? g[2] : 1.0f;
+    // branch-free 4-way select on the two gain bits (ptxas turns the plain ternaries into branches):
+    // bit0 picks within {g0|g1} and {none|g2}, bit1 picks between the pairs
+    const uint32_t b0 = gb & 1u, b1 = gb >> 1;
+    const float ped = selp(selp(p[2], 0.0f, b0), selp(p[1], p[0], b0), b1);
+    const float gf  = selp(selp(g[2], 1.0f, b0), selp(g[1], g[0], b0), b1);
     float off = 0.0f;
-    if (HAS_OFFS) off = is0 ? o[0] : is1 ? o[1] : is3 ? o[2] : 0.0f;
+    if (HAS_OFFS) off = selp(selp(o[2], 0.0f, b0), selp(o[1], o[0], b0), b1);
     x = __fsub_rn(x, ped);                                       // arrf[gr] -= peds[i][gr]   (x - 0 is exact)
     if (HAS_OFFS) x = __fsub_rn(x, off);                         // arrf -= offset, separately rounded
     float r = __fmul_rn(__fmul_rn(x, gf), maskf(fl));

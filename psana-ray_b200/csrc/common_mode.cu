@@ -99,11 +99,14 @@ __device__ __forceinline__ void block_kth_pass(const uint32_t (&key)[NKEY], uint
     constexpr int HSHIFT = PASS == 1 ? 21 : 10;                         // bits above the digit (PASS > 0)
     constexpr uint32_t DMASK = PASS == 2 ? 0x3FFu : 0x7FFu;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t haddr = (uint32_t)__cvta_generic_to_shared(hist);
 #pragma unroll
     for (int i = 0; i < NKEY; ++i) {
-        bool m = (elig >> i) & 1u;
-        if (PASS > 0) m = m && ((key[i] >> HSHIFT) == prefix);
-        if (m) atomicAdd(&hist[(key[i] >> SHIFT) & DMASK], 1u);
+        uint32_t m = (elig >> i) & 1u;
+        if (PASS > 0) m &= ((key[i] >> HSHIFT) == prefix) ? 1u : 0u;
+        // predicated shared-memory reduction: no branch around the atomic
+        asm volatile("{ .reg .pred q; setp.ne.u32 q, %1, 0; @q red.shared.add.u32 [%0], 1; }"
+                     :: "r"(haddr + (((key[i] >> SHIFT) & DMASK) << 2)), "r"(m) : "memory");
     }
     __syncthreads();
     uint32_t b[BPT]; uint32_t s = 0;
@@ -379,7 +382,7 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     float* outf = out + (size_t)frame * c.npix;
 
     uint32_t key[NK];
-    uint32_t elig = 0, sel0 = 0, sel1 = 0, mbits = 0, kbits = 0;
+    uint32_t elig = 0, sel0 = 0, sel1 = 0;
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
         const int ch = tid + j * NT;
@@ -418,9 +421,8 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
             }
             key[q] = psr_f2key(x);
             elig |= (el ? 1u : 0u) << q;
-            sel0 |= (sel & 1u) << q; sel1 |= (sel >> 1) << q;
-            mbits |= (f & PSR_FL_MASK ? 1u : 0u) << q;
-            kbits |= (f & PSR_FL_KEEP ? 1u : 0u) << q;
+            sel0 |= (sel & 1u) << q;
+            if (DET != 0) sel1 |= (sel >> 1) << q;
         }
     }
 
@@ -453,18 +455,20 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
         float ga[8], gb_[8], gc[8];
         if (DET == 0) { ld8(c.gf0 + gp, ga); ld8(c.gf1 + gp, gb_); }
         else { ld8(c.gfac + gp, ga); ld8(c.gfac + c.npix + gp, gb_); ld8(c.gfac + 2 * (size_t)c.npix + gp, gc); }
+        const uint2 fv = __ldg(reinterpret_cast<const uint2*>(c.flags + gp));       // L1/L2 hit: read in the load phase
         float o[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const int q = j * 8 + i;
+            const uint32_t f = ((i < 4 ? fv.x : fv.y) >> (8 * (i & 3))) | (c.ignore_keep ? PSR_FL_KEEP : 0u);
             float x = psr_key2f(key[q]);
             if (apply && ((elig >> q) & 1u)) x = __fsub_rn(x, cm);
             const uint32_t sel = ((sel0 >> q) & 1u) | (((sel1 >> q) & 1u) << 1);
             float gf;
             if (DET == 0) gf = sel ? gb_[i] : ga[i];
             else gf = sel == 0 ? ga[i] : sel == 1 ? gb_[i] : sel == 2 ? gc[i] : 1.0f;
-            const float v = __fmul_rn(__fmul_rn(x, gf), ((mbits >> q) & 1u) ? 1.0f : 0.0f);
-            o[i] = ((kbits >> q) & 1u) ? v : 0.0f;
+            const float v = __fmul_rn(__fmul_rn(x, gf), (f & PSR_FL_MASK) ? 1.0f : 0.0f);
+            o[i] = (f & PSR_FL_KEEP) ? v : 0.0f;
         }
         __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
         __stcs(reinterpret_cast<float4*>(outf + gp + 4), make_float4(o[4], o[5], o[6], o[7]));

@@ -53,6 +53,9 @@ def parse_arguments(argv=None):
                         help="Event source: seeded synthetic frames (default) or a real psana run")
     parser.add_argument("--num_events", type=int, default=1024, help="Synthetic source: events in the run (all ranks)")
     parser.add_argument("--common_mode", type=str, default=None, help="cmpars as 'alg,mode,cormax[,npix_min]'")
+    parser.add_argument("--reliable_sentinels", action="store_true",
+                        help="Retry the end-of-stream sentinels with the put back-off instead of dropping them when the queue is full "
+                             "(the reference drops them: producer.py:125 ignores put's result)")
     parser.add_argument("--device", type=int, default=None, help="CUDA device (default: local rank %% device count)")
     return parser.parse_args(argv)
 
@@ -240,7 +243,7 @@ def _backoff_put(queue, item, weight, lease, rank, what):
             time.sleep(1)
 
 
-def produce_data(source, pipeline, queue, world, num_consumers=1, max_steps=None, sleep=time.sleep):
+def produce_data(source, pipeline, queue, world, num_consumers=1, max_steps=None, sleep=time.sleep, reliable_sentinels=False):
     """The reference's ``produce_data`` (ref: producer.py:78-130) with events grouped into batches.
 
     ``pipeline`` needs ``batch_size``, ``stage(k, raw)``, ``process(n, queue) -> (payload, lease) | None``."""
@@ -290,7 +293,11 @@ def produce_data(source, pipeline, queue, world, num_consumers=1, max_steps=None
         # result of put is not checked, so a full queue drops sentinels (ref: producer.py:121-125)
         try:
             for _ in range(num_consumers):
-                queue.put(None)
+                if reliable_sentinels:
+                    if not _backoff_put(queue, None, 1, None, rank, "sentinel"):
+                        break
+                else:
+                    queue.put(None)
             logging.info(f"Rank 0: {num_consumers} sentinel values sent successfully")
         except QueueDeadError:
             logging.info("Rank 0: Queue actor is dead. Unable to send sentinels.")
@@ -343,7 +350,8 @@ def main(argv=None):
         manual = np.load(args.manual_mask_path) if args.manual_mask_path is not None else None
         nslabs = max(2, -(-args.queue_size // args.batch_size)) + 2
         pipeline = GpuBatchPipeline(source, psana_mode, device, args.batch_size, nslabs, bad, manual)
-        produce_data(source, pipeline, queue, world, args.num_consumers, args.max_steps)
+        produce_data(source, pipeline, queue, world, args.num_consumers, args.max_steps,
+                     reliable_sentinels=args.reliable_sentinels)
     except Exception as e:
         logging.error(f"Rank {rank}: Unhandled exception in main: {e}")
         logging.error("Traceback:")

@@ -297,6 +297,16 @@ def test_backoff_schedule_and_dropped_sentinels(qroot, monkeypatch):
     src = SyntheticSource("exp", 1, "epix10k2M", num_events=0, nseg=1)
     P.produce_data(src, OraclePipeline(src, ImageRetrievalMode.calib, 4), h, P.World(0, 1, 0), num_consumers=3)
     assert h.size() == 2 and h.stats()["refused"] >= 3
+    # additive --reliable_sentinels: sentinels wait for room like events do
+    state["n"] = -100
+    drained = []
+
+    def fake_sleep2(s):
+        drained.append(h.get())
+    monkeypatch.setattr(P.time, "sleep", fake_sleep2)
+    P.produce_data(src, OraclePipeline(src, ImageRetrievalMode.calib, 4), h, P.World(0, 1, 0), num_consumers=3, reliable_sentinels=True)
+    rest = [h.get() for _ in range(h.size())]
+    assert (drained + rest).count(None) == 3
 
 
 def test_dead_queue_makes_the_producer_return(qroot):
