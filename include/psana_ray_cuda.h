@@ -100,8 +100,8 @@ int psr_set_keep_mask(psr_ctx* ctx, const uint8_t* h_keep, size_t n, int out_kin
 int psr_reserve(psr_ctx* ctx, int max_frames);
 
 /* Tuning knobs that change speed, never results.  "frames_per_block": frames one CTA of the
- * streaming kernels walks with its constants held in registers (0 = auto: 32 for epix10ka, whose
- * 36.8 MB table stays L2-resident; the whole batch for jungfrau, whose 151 MB do not fit L2). */
+ * streaming kernels walks with its constants held in registers: 0 = auto (whole batch, at most 64),
+ * > 0 = that many, < 0 = persistent schedule (one equal share of the batch per resident CTA). */
 int psr_set_option(psr_ctx* ctx, const char* name, int value);
 
 /* THE HOT CALL.  Replaces, for a whole batch at once, det.calib(evt) / det.image(evt) inside

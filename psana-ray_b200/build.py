@@ -23,6 +23,7 @@ NVCC_FLAGS = [
     "-lineinfo", "-O3", "-std=c++17",
     "--fmad=false",                 # belt and braces: every float op is an explicit _rn intrinsic anyway
     "-Xcompiler", "-fPIC", "-shared",
+    "-Xlinker", "-Bsymbolic",       # internal calls bind inside the library, whatever else the process has loaded
     "-Xptxas", "-v",
 ]
 
@@ -40,6 +41,19 @@ def up_to_date() -> bool:
     t = os.path.getmtime(LIB)
     deps = [os.path.join(CSRC, s) for s in SOURCES] + HEADERS + [os.path.abspath(__file__)]
     return all(os.path.getmtime(d) <= t for d in deps)
+
+
+def build_variant(name: str, defines: dict) -> str:
+    """A tuning variant of the library (-D knobs) under lib/variants/, for sweeps on the GPU box."""
+    vdir = os.path.join(LIBDIR, "variants")
+    os.makedirs(vdir, exist_ok=True)
+    out = os.path.join(vdir, f"libpsana_ray_cuda.{name}.so")
+    flags = [f for f in NVCC_FLAGS if f not in ("-Xptxas", "-v")]
+    cmd = [find_nvcc()] + flags + [f"-D{k}={v}" for k, v in defines.items()] + [os.path.join(CSRC, s) for s in SOURCES] + ["-o", out]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + (res.stdout + res.stderr)[-4000:])
+    return out
 
 
 def build_library(force: bool = False, verbose: bool = False) -> str:

@@ -17,8 +17,57 @@
 
 namespace {
 
-constexpr int MAP_THREADS = 256;
-constexpr int MAP_UNROLL = 4;       // frames in flight per thread
+// tuning knobs (profiles/ holds the sweep that chose the defaults)
+#ifndef PSR_MAP_THREADS
+#define PSR_MAP_THREADS 256
+#endif
+#ifndef PSR_MAP_UNROLL
+#define PSR_MAP_UNROLL 8
+#endif
+#ifndef PSR_MAP_MINB
+#define PSR_MAP_MINB 4
+#endif
+#ifndef PSR_MAP_GROUPS      /* 4-pixel groups per thread in the epix10ka map kernel */
+#define PSR_MAP_GROUPS 1
+#endif
+#ifndef PSR_MAP_LD          /* raw loads: 0 ld.global.nc, 1 .cs (evict-first), 2 .nc.L1::no_allocate, 3 .cv */
+#define PSR_MAP_LD 1
+#endif
+#ifndef PSR_MAP_ST          /* out stores: 0 plain, 1 .cs, 2 .wt, 3 .L1::no_allocate */
+#define PSR_MAP_ST 1
+#endif
+#ifndef PSR_JF_THREADS
+#define PSR_JF_THREADS 128
+#endif
+#ifndef PSR_JF_UNROLL
+#define PSR_JF_UNROLL 4
+#endif
+constexpr int MAP_THREADS = PSR_MAP_THREADS;
+constexpr int JF_THREADS = PSR_JF_THREADS;
+constexpr int MAP_UNROLL = PSR_MAP_UNROLL;       // frames in flight per thread
+
+__device__ __forceinline__ uint2 ld_raw(const uint2* p) {
+#if PSR_MAP_LD == 0
+    return __ldg(p);
+#elif PSR_MAP_LD == 1
+    return __ldcs(p);
+#elif PSR_MAP_LD == 2
+    uint2 r; asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p)); return r;
+#else
+    return __ldcv(p);
+#endif
+}
+__device__ __forceinline__ void st_out(float4* p, const float4& v) {
+#if PSR_MAP_ST == 0
+    *p = v;
+#elif PSR_MAP_ST == 1
+    __stcs(p, v);
+#elif PSR_MAP_ST == 2
+    __stwt(p, v);
+#else
+    asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+#endif
+}
 template <int N> struct IntC { static constexpr int value = N; };
 
 __device__ __forceinline__ float maskf(uint32_t flbyte) { return (flbyte & PSR_FL_MASK) ? 1.0f : 0.0f; }
@@ -58,73 +107,101 @@ __device__ __forceinline__ float jf_px(uint32_t v, const float* p, const float* 
 
 __device__ __forceinline__ float f4get(const float4& v, int i) { return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w; }
 
+// Work of a map kernel = ntiles pixel tiles x nframes frames.  Two schedules:
+//   grid      (PERSIST = false): CTA (x, y) owns tile x and the frame chunk [y*fpb, (y+1)*fpb)
+//   persistent (PERSIST = true): the grid is exactly the number of CTAs the GPU holds at once (SMs x
+//     resident CTAs) and the linearised (tile, frame) space is cut into equal contiguous shares, so all
+//     SMs start together and finish together (no partial last wave); a CTA reloads the tile constants
+//     only when its share crosses a tile boundary.
+template <bool PERSIST, typename F>
+__device__ __forceinline__ void map_schedule(F&& do_tile, int nframes, int fpb, int ntiles) {
+    if (!PERSIST) {
+        const int f_begin = blockIdx.y * fpb;
+        do_tile((int)blockIdx.x, f_begin, min(nframes, f_begin + fpb));
+    } else {
+        const long long total = (long long)ntiles * nframes;
+        long long w = total * blockIdx.x / gridDim.x;
+        const long long w_end = total * (blockIdx.x + 1) / gridDim.x;
+        while (w < w_end) {
+            const int tile = (int)(w / nframes), f = (int)(w - (long long)tile * nframes);
+            const int f_end = (int)min((long long)nframes, f + (w_end - w));
+            do_tile(tile, f, f_end);
+            w += f_end - f;
+        }
+    }
+}
+
 // =================================================================================================
 // K1: epix10ka calib map.  A warp covers 64 groups of 4 pixels; lane L owns groups L and L+32 so
 // that both the 8-byte raw loads and the 16-byte output stores of a warp instruction are contiguous.
 // =================================================================================================
-__global__ void __launch_bounds__(MAP_THREADS, 3)
+template <bool PERSIST>
+__global__ void __launch_bounds__(MAP_THREADS, PSR_MAP_MINB)
 epix_calib_map_kernel(const uint2* __restrict__ raw, float4* __restrict__ out,
                       const float4* __restrict__ ped0, const float4* __restrict__ gf0,
                       const float4* __restrict__ ped1, const float4* __restrict__ gf1,
-                      const uint32_t* __restrict__ flags, int ngroups, int nframes, int fpb)
+                      const uint32_t* __restrict__ flags, int ngroups, int nframes, int fpb, int ntiles)
 {
+    constexpr int NG = PSR_MAP_GROUPS;                 // 4-pixel groups per thread
     const int lane = threadIdx.x & 31;
-    const int wbase = (blockIdx.x * MAP_THREADS + (threadIdx.x & ~31)) * 2;
-    const int g0i = wbase + lane, g1i = wbase + 32 + lane;
-    const bool ok0 = g0i < ngroups, ok1 = g1i < ngroups;
-    if (!ok0) return;
-    const int f_begin = blockIdx.y * fpb;
-    const int f_end = min(nframes, f_begin + fpb);
+    auto do_tile = [&](int tile, int f_begin, int f_end) {
+    const int wbase = (tile * MAP_THREADS + (threadIdx.x & ~31)) * NG;
+    if (wbase + lane >= ngroups) return;
 
-    float4 p0[2], q0[2], p1[2], q1[2]; uint32_t fl[2];
-    p0[0] = __ldg(ped0 + g0i); q0[0] = __ldg(gf0 + g0i); p1[0] = __ldg(ped1 + g0i); q1[0] = __ldg(gf1 + g0i); fl[0] = __ldg(flags + g0i);
-    if (ok1) { p0[1] = __ldg(ped0 + g1i); q0[1] = __ldg(gf0 + g1i); p1[1] = __ldg(ped1 + g1i); q1[1] = __ldg(gf1 + g1i); fl[1] = __ldg(flags + g1i); }
-    else     { p0[1] = p0[0]; q0[1] = q0[0]; p1[1] = p1[0]; q1[1] = q1[0]; fl[1] = fl[0]; }
-    const int gi[2] = {g0i, ok1 ? g1i : g0i};
+    float4 p0[NG], q0[NG], p1[NG], q1[NG]; uint32_t fl[NG]; int gi[NG]; bool ok[NG];
+#pragma unroll
+    for (int h = 0; h < NG; ++h) {
+        const int g = wbase + lane + 32 * h;
+        ok[h] = g < ngroups;
+        gi[h] = ok[h] ? g : wbase + lane;
+        p0[h] = __ldg(ped0 + gi[h]); q0[h] = __ldg(gf0 + gi[h]); p1[h] = __ldg(ped1 + gi[h]); q1[h] = __ldg(gf1 + gi[h]);
+        fl[h] = __ldg(flags + gi[h]);
+    }
 
     auto frames = [&](int f, auto nconst) {           // nconst frames starting at f, loads first, then math + stores
         constexpr int NF = decltype(nconst)::value;
-        uint2 r[NF][2];
+        uint2 r[NF][NG];
 #pragma unroll
         for (int u = 0; u < NF; ++u) {
             const size_t base = (size_t)(f + u) * ngroups;
-            r[u][0] = __ldcs(raw + base + gi[0]);
-            r[u][1] = __ldcs(raw + base + gi[1]);
+#pragma unroll
+            for (int h = 0; h < NG; ++h) r[u][h] = ld_raw(raw + base + gi[h]);
         }
 #pragma unroll
         for (int u = 0; u < NF; ++u) {
             const size_t base = (size_t)(f + u) * ngroups;
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                if (h == 1 && !ok1) break;
+            for (int h = 0; h < NG; ++h) {
+                if (h > 0 && !ok[h]) break;
                 const uint32_t a = r[u][h].x, b = r[u][h].y;
                 float4 o;
                 o.x = epix_px(a & 0xFFFFu, p0[h].x, q0[h].x, p1[h].x, q1[h].x, fl[h]);
                 o.y = epix_px(a >> 16,     p0[h].y, q0[h].y, p1[h].y, q1[h].y, fl[h] >> 8);
                 o.z = epix_px(b & 0xFFFFu, p0[h].z, q0[h].z, p1[h].z, q1[h].z, fl[h] >> 16);
                 o.w = epix_px(b >> 16,     p0[h].w, q0[h].w, p1[h].w, q1[h].w, fl[h] >> 24);
-                __stcs(out + base + gi[h], o);
+                st_out(out + base + gi[h], o);
             }
         }
     };
     int f = f_begin;
     for (; f + MAP_UNROLL <= f_end; f += MAP_UNROLL) frames(f, IntC<MAP_UNROLL>{});
     for (; f < f_end; ++f) frames(f, IntC<1>{});
+    };
+    map_schedule<PERSIST>(do_tile, nframes, fpb, ntiles);
 }
 
 // =================================================================================================
 // K2: jungfrau calib map.  One group of 4 pixels per thread (9 float4 of constants = 36 registers).
 // =================================================================================================
-template <bool HAS_OFFS>
-__global__ void __launch_bounds__(MAP_THREADS)
+template <bool HAS_OFFS, bool PERSIST>
+__global__ void __launch_bounds__(JF_THREADS)
 jf_calib_map_kernel(const uint2* __restrict__ raw, float4* __restrict__ out,
                     const float4* __restrict__ peds, const float4* __restrict__ offs, const float4* __restrict__ gfac,
-                    const uint32_t* __restrict__ flags, int ngroups, int nframes, int fpb)
+                    const uint32_t* __restrict__ flags, int ngroups, int nframes, int fpb, int ntiles)
 {
-    const int g = blockIdx.x * MAP_THREADS + threadIdx.x;
+    auto do_tile = [&](int tile, int f_begin, int f_end) {
+    const int g = tile * JF_THREADS + threadIdx.x;
     if (g >= ngroups) return;
-    const int f_begin = blockIdx.y * fpb;
-    const int f_end = min(nframes, f_begin + fpb);
     float P[4][3], O[4][3], G[4][3];
 #pragma unroll
     for (int m = 0; m < 3; ++m) {
@@ -141,7 +218,7 @@ jf_calib_map_kernel(const uint2* __restrict__ raw, float4* __restrict__ out,
         constexpr int NF = decltype(nconst)::value;
         uint2 r[NF];
 #pragma unroll
-        for (int u = 0; u < NF; ++u) r[u] = __ldcs(raw + (size_t)(f + u) * ngroups + g);
+        for (int u = 0; u < NF; ++u) r[u] = ld_raw(raw + (size_t)(f + u) * ngroups + g);
 #pragma unroll
         for (int u = 0; u < NF; ++u) {
             float4 o;
@@ -149,12 +226,14 @@ jf_calib_map_kernel(const uint2* __restrict__ raw, float4* __restrict__ out,
             o.y = jf_px<HAS_OFFS>(r[u].x >> 16,     P[1], O[1], G[1], fl >> 8);
             o.z = jf_px<HAS_OFFS>(r[u].y & 0xFFFFu, P[2], O[2], G[2], fl >> 16);
             o.w = jf_px<HAS_OFFS>(r[u].y >> 16,     P[3], O[3], G[3], fl >> 24);
-            __stcs(out + (size_t)(f + u) * ngroups + g, o);
+            st_out(out + (size_t)(f + u) * ngroups + g, o);
         }
     };
     int f = f_begin;
-    for (; f + MAP_UNROLL <= f_end; f += MAP_UNROLL) frames(f, IntC<MAP_UNROLL>{});
+    for (; f + PSR_JF_UNROLL <= f_end; f += PSR_JF_UNROLL) frames(f, IntC<PSR_JF_UNROLL>{});
     for (; f < f_end; ++f) frames(f, IntC<1>{});
+    };
+    map_schedule<PERSIST>(do_tile, nframes, fpb, ntiles);
 }
 
 // =================================================================================================
@@ -275,32 +354,60 @@ image_fused_kernel(const uint16_t* __restrict__ raw, float* __restrict__ img, Ps
 }  // namespace
 
 // ---- launchers --------------------------------------------------------------------------------
+namespace {
+template <typename K>
+int resident_ctas(K kernel, int threads) {          // SMs x CTAs resident per SM for this kernel on the current device
+    int dev = 0, sms = 0, per = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, kernel, threads, 0);
+    return sms * (per > 0 ? per : 1);
+}
+}  // namespace
+
+// fpb > 0: grid schedule with that many frames per CTA; fpb == 0: grid schedule, whole batch (<= 64 frames) per CTA --
+// the measured best (profiles/README.md); fpb < 0: persistent balanced schedule
 cudaError_t psr_launch_calib_map(const PsrDev& c, const uint16_t* d_raw, int nframes, float* d_out,
                                  int fpb, cudaStream_t st)
 {
     if (nframes <= 0) return cudaSuccess;
     const int ngroups = c.npix / 4;
-    if (fpb <= 0 || fpb > nframes) fpb = nframes;
+    const bool persist = fpb < 0;
+    if (fpb == 0) fpb = nframes < 64 ? nframes : 64;
+    if (fpb < 0 || fpb > nframes) fpb = nframes;
     const int ysplit = (nframes + fpb - 1) / fpb;
+    const uint2* raw = reinterpret_cast<const uint2*>(d_raw);
+    float4* out = reinterpret_cast<float4*>(d_out);
+    const uint32_t* fl = reinterpret_cast<const uint32_t*>(c.flags);
     if (c.det_kind == 0) {
-        dim3 grid((ngroups + 2 * MAP_THREADS - 1) / (2 * MAP_THREADS), ysplit);
-        epix_calib_map_kernel<<<grid, MAP_THREADS, 0, st>>>(
-            reinterpret_cast<const uint2*>(d_raw), reinterpret_cast<float4*>(d_out),
-            reinterpret_cast<const float4*>(c.ped0), reinterpret_cast<const float4*>(c.gf0),
-            reinterpret_cast<const float4*>(c.ped1), reinterpret_cast<const float4*>(c.gf1),
-            reinterpret_cast<const uint32_t*>(c.flags), ngroups, nframes, fpb);
+        const int ntiles = (ngroups + PSR_MAP_GROUPS * MAP_THREADS - 1) / (PSR_MAP_GROUPS * MAP_THREADS);
+        const float4 *a0 = reinterpret_cast<const float4*>(c.ped0), *a1 = reinterpret_cast<const float4*>(c.gf0);
+        const float4 *a2 = reinterpret_cast<const float4*>(c.ped1), *a3 = reinterpret_cast<const float4*>(c.gf1);
+        if (persist) {
+            static int nres = 0;
+            if (!nres) nres = resident_ctas(epix_calib_map_kernel<true>, MAP_THREADS);
+            const long long total = (long long)ntiles * nframes;
+            const int grid = (int)(total < nres ? total : nres);
+            epix_calib_map_kernel<true><<<grid, MAP_THREADS, 0, st>>>(raw, out, a0, a1, a2, a3, fl, ngroups, nframes, fpb, ntiles);
+        } else {
+            epix_calib_map_kernel<false><<<dim3(ntiles, ysplit), MAP_THREADS, 0, st>>>(raw, out, a0, a1, a2, a3, fl, ngroups, nframes, fpb, ntiles);
+        }
     } else {
-        dim3 grid((ngroups + MAP_THREADS - 1) / MAP_THREADS, ysplit);
-        if (c.offs != nullptr)
-            jf_calib_map_kernel<true><<<grid, MAP_THREADS, 0, st>>>(
-                reinterpret_cast<const uint2*>(d_raw), reinterpret_cast<float4*>(d_out),
-                reinterpret_cast<const float4*>(c.peds), reinterpret_cast<const float4*>(c.offs),
-                reinterpret_cast<const float4*>(c.gfac), reinterpret_cast<const uint32_t*>(c.flags), ngroups, nframes, fpb);
-        else
-            jf_calib_map_kernel<false><<<grid, MAP_THREADS, 0, st>>>(
-                reinterpret_cast<const uint2*>(d_raw), reinterpret_cast<float4*>(d_out),
-                reinterpret_cast<const float4*>(c.peds), nullptr,
-                reinterpret_cast<const float4*>(c.gfac), reinterpret_cast<const uint32_t*>(c.flags), ngroups, nframes, fpb);
+        const int ntiles = (ngroups + JF_THREADS - 1) / JF_THREADS;
+        const float4 *p = reinterpret_cast<const float4*>(c.peds), *o = reinterpret_cast<const float4*>(c.offs);
+        const float4 *g = reinterpret_cast<const float4*>(c.gfac);
+        const long long total = (long long)ntiles * nframes;
+#define PSR_JF_LAUNCH(OFFS)                                                                                          \
+        if (persist) {                                                                                               \
+            static int nres = 0;                                                                                     \
+            if (!nres) nres = resident_ctas(jf_calib_map_kernel<OFFS, true>, JF_THREADS);                          \
+            const int grid = (int)(total < nres ? total : nres);                                                     \
+            jf_calib_map_kernel<OFFS, true><<<grid, JF_THREADS, 0, st>>>(raw, out, p, o, g, fl, ngroups, nframes, fpb, ntiles); \
+        } else {                                                                                                     \
+            jf_calib_map_kernel<OFFS, false><<<dim3(ntiles, ysplit), JF_THREADS, 0, st>>>(raw, out, p, o, g, fl, ngroups, nframes, fpb, ntiles); \
+        }
+        if (c.offs != nullptr) { PSR_JF_LAUNCH(true) } else { PSR_JF_LAUNCH(false) }
+#undef PSR_JF_LAUNCH
     }
     return cudaGetLastError();
 }

@@ -84,7 +84,7 @@ struct psr_ctx {
     int32_t* d_inv = nullptr;
     uint8_t* d_keep_image = nullptr;
     float* d_scratch = nullptr; size_t scratch_elems = 0;
-    int frames_per_block = 0;      // 0 = auto: epix10ka 32 (constants L2-resident), jungfrau whole batch (151 MB of constants do not fit L2)
+    int frames_per_block = 0;      // 0 = auto: persistent balanced schedule; > 0 forces the (tile, frame chunk) grid
     HostPipe pipe;
 };
 
@@ -133,7 +133,7 @@ int ensure_scratch(psr_ctx* c, size_t elems) {
 
 int launch_batch(psr_ctx* c, const uint16_t* d_raw, int nframes, float* d_out, int out_kind, cudaStream_t st) {
     const PsrDev& d = c->dev;
-    const int fpb = c->frames_per_block > 0 ? c->frames_per_block : (d.det_kind == PSR_DET_EPIX10KA ? 32 : nframes);
+    const int fpb = c->frames_per_block;      // 0 = persistent balanced schedule (map kernels); image gather: whole batch per CTA
     if (out_kind == PSR_OUT_CALIB) {
         if (d.cm_mode == 0) PSR_CUDA(psr_launch_calib_map(d, d_raw, nframes, d_out, fpb, st));
         else                PSR_CUDA(psr_launch_common_mode(d, d_raw, nframes, d_out, st));
@@ -359,7 +359,7 @@ int psr_reserve(psr_ctx* c, int max_frames) {
 
 int psr_set_option(psr_ctx* c, const char* name, int value) {
     if (!c || !name) return fail(PSR_E_INVALID, "null argument");
-    if (!strcmp(name, "frames_per_block")) { if (value <= 0) return fail(PSR_E_INVALID, "frames_per_block must be > 0"); c->frames_per_block = value; return PSR_OK; }
+    if (!strcmp(name, "frames_per_block")) { c->frames_per_block = value; return PSR_OK; }
     return fail(PSR_E_INVALID, "unknown option %s", name);
 }
 

@@ -26,6 +26,25 @@ __device__ __forceinline__ void ld8(const float* __restrict__ p, float (&d)[8]) 
     d[0] = u.x; d[1] = u.y; d[2] = u.z; d[3] = u.w; d[4] = v.x; d[5] = v.y; d[6] = v.z; d[7] = v.w;
 }
 
+// CW (4 or 8) consecutive floats / raw pixels / flag bytes into registers
+template <int CW>
+__device__ __forceinline__ void ldN(const float* __restrict__ p, float (&d)[8]) {
+    const float4 u = __ldg(reinterpret_cast<const float4*>(p));
+    d[0] = u.x; d[1] = u.y; d[2] = u.z; d[3] = u.w;
+    if (CW == 8) { const float4 v = __ldg(reinterpret_cast<const float4*>(p) + 1); d[4] = v.x; d[5] = v.y; d[6] = v.z; d[7] = v.w; }
+}
+template <int CW>
+__device__ __forceinline__ void ld_flags(const uint8_t* __restrict__ fl, uint32_t (&fw)[2]) {
+    if (CW == 8) { const uint2 f = __ldg(reinterpret_cast<const uint2*>(fl)); fw[0] = f.x; fw[1] = f.y; }
+    else { fw[0] = __ldg(reinterpret_cast<const uint32_t*>(fl)); fw[1] = 0; }
+}
+template <int CW>
+__device__ __forceinline__ void ld_raw_flags(const uint16_t* __restrict__ raw, const uint8_t* __restrict__ fl, uint32_t (&w)[4], uint32_t (&fw)[2]) {
+    if (CW == 8) { const uint4 r = __ldcs(reinterpret_cast<const uint4*>(raw)); w[0] = r.x; w[1] = r.y; w[2] = r.z; w[3] = r.w; }
+    else { const uint2 r = __ldcs(reinterpret_cast<const uint2*>(raw)); w[0] = r.x; w[1] = r.y; w[2] = w[3] = 0; }
+    ld_flags<CW>(fl, fw);
+}
+
 template <int NW>
 struct BlockRed {
     int* buf;      // [2][32]
@@ -89,7 +108,7 @@ __device__ __forceinline__ float warp_median(const uint32_t (&key)[NK], int n) {
 // ---- CTA-wide exact selection: 3-pass radix select (11 + 11 + 10 bits) on a 2048-bin shared histogram.
 // Keys stay in registers; bit i of `elig` says key[i] takes part.  Returns the k-th smallest (0-based)
 // eligible key; k must be < the number of eligible keys.  Every thread of the CTA must call it.
-// hist: 2048 words of shared memory; sh: 34 ints of shared memory.
+// hist: 2048 words of shared memory; sh: 40 ints of shared memory (sh[34] = population of the chosen bin).
 template <int NT, int NKEY, int PASS>
 __device__ __forceinline__ void block_kth_pass(const uint32_t (&key)[NKEY], uint32_t elig, uint32_t& prefix, int& k,
                                                uint32_t* hist, int* sh)
@@ -130,7 +149,7 @@ __device__ __forceinline__ void block_kth_pass(const uint32_t (&key)[NKEY], uint
         uint32_t r = (uint32_t)k - excl; int bin = tid * BPT; bool done = false;
 #pragma unroll
         for (int j = 0; j < BPT; ++j) {
-            if (!done) { if (r < b[j]) { bin = tid * BPT + j; done = true; } else r -= b[j]; }
+            if (!done) { if (r < b[j]) { bin = tid * BPT + j; done = true; sh[34] = (int)b[j]; } else r -= b[j]; }
         }
         sh[32] = bin; sh[33] = (int)r;
     }
@@ -151,6 +170,119 @@ __device__ __forceinline__ uint32_t block_kth(const uint32_t (&key)[NKEY], uint3
     return prefix;
 }
 
+
+// ---- median of the CTA's eligible keys, fast path --------------------------------------------------
+// Pass 0 histograms all keys on their top 11 bits.  The bin holding the median usually holds a few
+// hundred keys; those are compacted into a shared list and only the list is refined: one more
+// 11-bit pass over the list, then the (typically < 32) survivors are ranked by one warp, which yields
+// both middle order statistics at once.  Anything unusual (list overflow, many survivors, the upper
+// middle value outside the survivors) falls back to the register passes -- same exact answer.
+constexpr int LISTCAP = 1024;
+
+template <int NT, int NK, int NW>
+__device__ __forceinline__ void block_median_keys(const uint32_t (&key)[NK], uint32_t elig, int n, uint32_t* hist, int* sh,
+                                                  uint32_t* list, BlockRed<NW>& red, uint32_t& lo_out, uint32_t& hi_out)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int k1 = (n - 1) >> 1, k2 = n >> 1;
+    for (int i = tid; i < 2048; i += NT) hist[i] = 0u;
+    if (tid == 0) { sh[35] = 0; sh[36] = 0; }
+    __syncthreads();
+    uint32_t prefix = 0; int k = k1;
+    block_kth_pass<NT, NK, 0>(key, elig, prefix, k, hist, sh);
+    const int M = sh[34];
+    bool have_lo = false, have_hi = false;
+    uint32_t lo = 0, hi = 0;
+    if (M <= LISTCAP) {                                         // uniform
+        // warp-aggregated append: one shared atomic per warp per step instead of one per matching key
+#pragma unroll
+        for (int i = 0; i < NK; ++i) {
+            const bool hit = ((elig >> i) & 1u) && (key[i] >> 21) == prefix;
+            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, hit);
+            if (bal) {
+                int base = 0;
+                if (lane == 0) base = atomicAdd(&sh[35], __popc(bal));
+                base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                if (hit) list[base + __popc(bal & ((1u << lane) - 1u))] = key[i];
+            }
+        }
+        __syncthreads();
+        // pass 1 over the list: bits 20..10
+        const uint32_t haddr = (uint32_t)__cvta_generic_to_shared(hist);
+        for (int i = tid; i < M; i += NT)
+            asm volatile("red.shared.add.u32 [%0], 1;" :: "r"(haddr + (((list[i] >> 10) & 0x7FFu) << 2)) : "memory");
+        __syncthreads();
+        {   // find the bin of rank k among the list (same scan as block_kth_pass, keys come from the list)
+            constexpr int NB = 2048, BPT = (NB + NT - 1) / NT;
+            uint32_t b[BPT]; uint32_t s = 0;
+#pragma unroll
+            for (int j = 0; j < BPT; ++j) { const int idx = tid * BPT + j; b[j] = idx < NB ? hist[idx] : 0u; if (idx < NB) hist[idx] = 0u; s += b[j]; }
+            uint32_t incl = s;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+            if (lane == 31) sh[warp] = (int)incl;
+            __syncthreads();
+            uint32_t base = 0;
+#pragma unroll
+            for (int w = 0; w < NW; ++w) base += (w < warp) ? (uint32_t)sh[w] : 0u;
+            const uint32_t excl = base + incl - s;
+            if ((uint32_t)k >= excl && (uint32_t)k < excl + s) {
+                uint32_t r = (uint32_t)k - excl; bool done = false;
+#pragma unroll
+                for (int j = 0; j < BPT; ++j)
+                    if (!done) { if (r < b[j]) { sh[32] = tid * BPT + j; sh[34] = (int)b[j]; done = true; } else r -= b[j]; }
+                sh[33] = (int)r;
+            }
+            __syncthreads();
+        }
+        const uint32_t prefix2 = (prefix << 11) | (uint32_t)sh[32];
+        const int r1 = sh[33], M1 = sh[34];
+        if (M1 <= 32) {                                         // uniform: survivors ranked by warp 0
+            uint32_t* list2 = list + LISTCAP;
+            for (int i = tid; i < M; i += NT)
+                if ((list[i] >> 10) == prefix2) list2[atomicAdd(&sh[36], 1)] = list[i];
+            __syncthreads();
+            if (warp == 0) {
+                const uint32_t v = lane < M1 ? list2[lane] : 0xFFFFFFFFu;
+                int rank = 0;
+                for (int j = 0; j < M1; ++j) {
+                    const uint32_t o = __shfl_sync(0xFFFFFFFFu, v, j);
+                    rank += (o < v) || (o == v && j < lane);
+                }
+                if (lane < M1 && rank == r1) sh[37] = (int)v;
+                if (lane < M1 && rank == r1 + 1) sh[38] = (int)v;
+            }
+            __syncthreads();
+            lo = (uint32_t)sh[37]; have_lo = true;
+            if (k2 == k1) { hi = lo; have_hi = true; }
+            else if (r1 + 1 < M1) { hi = (uint32_t)sh[38]; have_hi = true; }
+        } else {
+            prefix = prefix2; k = r1;                           // continue with the last register pass
+            uint32_t pfx = prefix2; int kk = r1;
+            block_kth_pass<NT, NK, 2>(key, elig, pfx, kk, hist, sh);
+            lo = pfx; have_lo = true;
+        }
+    } else {
+        block_kth_pass<NT, NK, 1>(key, elig, prefix, k, hist, sh);
+        block_kth_pass<NT, NK, 2>(key, elig, prefix, k, hist, sh);
+        lo = prefix; have_lo = true;
+    }
+    (void)have_lo;
+    if (!have_hi) {
+        hi = lo;
+        if (k2 != k1) {
+            int cle = 0; uint32_t mg = 0xFFFFFFFFu;
+#pragma unroll
+            for (int i = 0; i < NK; ++i)
+                if ((elig >> i) & 1u) { cle += (key[i] <= lo); if (key[i] > lo) mg = min(mg, key[i]); }
+            cle = red.sum(cle);
+            mg = red.minu(mg);
+            if (cle <= k2) hi = mg;
+        }
+    }
+    lo_out = lo; hi_out = hi;
+}
+
 // smem flag byte of a tile pixel: bit0 mask, bit1 eligible (this frame), bit3 keep, bits 4-5 gain selector
 //   epix10ka selector: data bit 14;  jungfrau selector: 0,1,2 = g0,g1,g2, 3 = none
 template <int DET, int ROWS, int COLS, int NB, int NT>
@@ -166,7 +298,7 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     uint8_t* fl = reinterpret_cast<uint8_t*>(a + TR * ST);     // TR * ST
     __shared__ int redbuf[64];
     __shared__ uint32_t hist[2048];
-    __shared__ int selsh[34];
+    __shared__ int selsh[40];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int bid = blockIdx.x;
@@ -361,16 +493,17 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
 // thread keeps the keys of its CPT*8 pixels in registers from load to store; eligibility, gain
 // selector, mask and keep bits are packed in four 32-bit registers.
 // =================================================================================================
-template <int DET, int ROWS, int COLS, int NB, int NT, int MINB>
+template <int DET, int ROWS, int COLS, int NB, int NT, int MINB, int CW>
 __global__ void __launch_bounds__(NT, MINB)
 cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c)
 {
-    constexpr int TR = ROWS / 2, TC = COLS / NB, CH = TC / 8, NCH = TR * CH, CPT = NCH / NT, NK = CPT * 8;
+    constexpr int TR = ROWS / 2, TC = COLS / NB, CH = TC / CW, NCH = TR * CH, CPT = NCH / NT, NK = CPT * CW;   // CW = pixels per chunk (4 or 8)
     constexpr int NW = NT / 32;
     static_assert(NCH % NT == 0 && NT % 32 == 0 && NK <= 32, "tile must split evenly over the CTA");
     __shared__ int redbuf[64];
     __shared__ uint32_t hist[2048];
-    __shared__ int selsh[34];
+    __shared__ uint32_t list[LISTCAP + 32];
+    __shared__ int selsh[40];
 
     const int tid = threadIdx.x;
     int bid = blockIdx.x;
@@ -387,21 +520,20 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     for (int j = 0; j < CPT; ++j) {
         const int ch = tid + j * NT;
         const int r = ch / CH, cc = ch - r * CH;
-        const int gp = ((seg * ROWS + half * TR + r) * COLS) + bank * TC + cc * 8;
-        const uint4 rv = __ldcs(reinterpret_cast<const uint4*>(rawf + gp));
-        const uint2 fv = __ldg(reinterpret_cast<const uint2*>(c.flags + gp));
-        const uint32_t w[4] = {rv.x, rv.y, rv.z, rv.w};
+        const int gp = ((seg * ROWS + half * TR + r) * COLS) + bank * TC + cc * CW;
+        uint32_t w[4], fw[2];
+        ld_raw_flags<CW>(rawf + gp, c.flags + gp, w, fw);
         float pa[8], pb[8], pc[8], oa[8], ob[8], oc[8];
-        if (DET == 0) { ld8(c.ped0 + gp, pa); ld8(c.ped1 + gp, pb); }
+        if (DET == 0) { ldN<CW>(c.ped0 + gp, pa); ldN<CW>(c.ped1 + gp, pb); }
         else {
-            ld8(c.peds + gp, pa); ld8(c.peds + c.npix + gp, pb); ld8(c.peds + 2 * (size_t)c.npix + gp, pc);
-            if (c.offs != nullptr) { ld8(c.offs + gp, oa); ld8(c.offs + c.npix + gp, ob); ld8(c.offs + 2 * (size_t)c.npix + gp, oc); }
+            ldN<CW>(c.peds + gp, pa); ldN<CW>(c.peds + c.npix + gp, pb); ldN<CW>(c.peds + 2 * (size_t)c.npix + gp, pc);
+            if (c.offs != nullptr) { ldN<CW>(c.offs + gp, oa); ldN<CW>(c.offs + c.npix + gp, ob); ldN<CW>(c.offs + 2 * (size_t)c.npix + gp, oc); }
         }
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const int q = j * 8 + i;
+        for (int i = 0; i < CW; ++i) {
+            const int q = j * CW + i;
             const uint32_t v = (i & 1) ? (w[i >> 1] >> 16) : (w[i >> 1] & 0xFFFFu);
-            const uint32_t f = (((i < 4 ? fv.x : fv.y) >> (8 * (i & 3))) & 0xFFu) | (c.ignore_keep ? PSR_FL_KEEP : 0u);
+            const uint32_t f = ((fw[i >> 2] >> (8 * (i & 3))) & 0xFFu) | (c.ignore_keep ? PSR_FL_KEEP : 0u);
             float x = (float)(v & 0x3FFFu);
             uint32_t sel, el;
             if (DET == 0) {
@@ -431,18 +563,8 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     const int n = red.sum(__popc(elig));
     float cm = 0.f; bool apply = false;
     if (n >= c.npix_min && n > 0) {                        // uniform across the CTA
-        const int k1 = (n - 1) >> 1, k2 = n >> 1;
-        const uint32_t lo = block_kth<NT, NK>(key, elig, k1, hist, selsh);
-        uint32_t hi = lo;
-        if (k2 != k1) {
-            int cle = 0; uint32_t mg = 0xFFFFFFFFu;
-#pragma unroll
-            for (int i = 0; i < NK; ++i)
-                if ((elig >> i) & 1u) { cle += (key[i] <= lo); if (key[i] > lo) mg = min(mg, key[i]); }
-            cle = red.sum(cle);
-            mg = red.minu(mg);
-            if (cle <= k2) hi = mg;
-        }
+        uint32_t lo, hi;
+        block_median_keys<NT, NK, NW>(key, elig, n, hist, selsh, list, red, lo, hi);
         cm = psr_mid(psr_key2f(lo), psr_key2f(hi));
         apply = !(fabsf(cm) > c.cormax);
     }
@@ -451,16 +573,17 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     for (int j = 0; j < CPT; ++j) {
         const int ch = tid + j * NT;
         const int r = ch / CH, cc = ch - r * CH;
-        const int gp = ((seg * ROWS + half * TR + r) * COLS) + bank * TC + cc * 8;
+        const int gp = ((seg * ROWS + half * TR + r) * COLS) + bank * TC + cc * CW;
         float ga[8], gb_[8], gc[8];
-        if (DET == 0) { ld8(c.gf0 + gp, ga); ld8(c.gf1 + gp, gb_); }
-        else { ld8(c.gfac + gp, ga); ld8(c.gfac + c.npix + gp, gb_); ld8(c.gfac + 2 * (size_t)c.npix + gp, gc); }
-        const uint2 fv = __ldg(reinterpret_cast<const uint2*>(c.flags + gp));       // L1/L2 hit: read in the load phase
+        if (DET == 0) { ldN<CW>(c.gf0 + gp, ga); ldN<CW>(c.gf1 + gp, gb_); }
+        else { ldN<CW>(c.gfac + gp, ga); ldN<CW>(c.gfac + c.npix + gp, gb_); ldN<CW>(c.gfac + 2 * (size_t)c.npix + gp, gc); }
+        uint32_t fw[2];
+        ld_flags<CW>(c.flags + gp, fw);                                              // L1/L2 hit: read in the load phase
         float o[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const int q = j * 8 + i;
-            const uint32_t f = ((i < 4 ? fv.x : fv.y) >> (8 * (i & 3))) | (c.ignore_keep ? PSR_FL_KEEP : 0u);
+        for (int i = 0; i < CW; ++i) {
+            const int q = j * CW + i;
+            const uint32_t f = (fw[i >> 2] >> (8 * (i & 3))) | (c.ignore_keep ? PSR_FL_KEEP : 0u);
             float x = psr_key2f(key[q]);
             if (apply && ((elig >> q) & 1u)) x = __fsub_rn(x, cm);
             const uint32_t sel = ((sel0 >> q) & 1u) | (((sel1 >> q) & 1u) << 1);
@@ -471,11 +594,16 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
             o[i] = (f & PSR_FL_KEEP) ? v : 0.0f;
         }
         __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
-        __stcs(reinterpret_cast<float4*>(outf + gp + 4), make_float4(o[4], o[5], o[6], o[7]));
+        if (CW == 8) __stcs(reinterpret_cast<float4*>(outf + gp + 4), make_float4(o[4], o[5], o[6], o[7]));
     }
 }
 
 constexpr int EPIX_NT = 352, JF_NT = 512;
+#ifndef PSR_CMB_EPIX_NT          /* banks-only kernel: threads, min CTAs/SM, pixels per chunk */
+#define PSR_CMB_EPIX_NT 352
+#define PSR_CMB_EPIX_MINB 2
+#define PSR_CMB_EPIX_CW 8
+#endif
 constexpr size_t EPIX_SMEM = (size_t)(176 * 49) * 5;     // float + flag byte per padded tile pixel
 constexpr size_t JF_SMEM = (size_t)(256 * 65) * 5;
 
@@ -495,11 +623,11 @@ cudaError_t psr_launch_common_mode(const PsrDev& c, const uint16_t* d_raw, int n
     if (nframes <= 0) return cudaSuccess;
     if (c.det_kind == 0) {
         const unsigned grid = (unsigned)nframes * c.nseg * 2 * 8;
-        if (c.cm_mode == 4) cm_banks_kernel<0, 352, 384, 8, EPIX_NT, 2><<<grid, EPIX_NT, 0, st>>>(d_raw, d_out, c);
+        if (c.cm_mode == 4) cm_banks_kernel<0, 352, 384, 8, PSR_CMB_EPIX_NT, PSR_CMB_EPIX_MINB, PSR_CMB_EPIX_CW><<<grid, PSR_CMB_EPIX_NT, 0, st>>>(d_raw, d_out, c);
         else cm_calib_kernel<0, 352, 384, 8, EPIX_NT><<<grid, EPIX_NT, EPIX_SMEM, st>>>(d_raw, d_out, c);
     } else {
         const unsigned grid = (unsigned)nframes * c.nseg * 2 * 16;
-        if (c.cm_mode == 4) cm_banks_kernel<1, 512, 1024, 16, JF_NT, 1><<<grid, JF_NT, 0, st>>>(d_raw, d_out, c);
+        if (c.cm_mode == 4) cm_banks_kernel<1, 512, 1024, 16, JF_NT, 1, 8><<<grid, JF_NT, 0, st>>>(d_raw, d_out, c);
         else cm_calib_kernel<1, 512, 1024, 16, JF_NT><<<grid, JF_NT, JF_SMEM, st>>>(d_raw, d_out, c);
     }
     return cudaGetLastError();

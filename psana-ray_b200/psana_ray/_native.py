@@ -86,7 +86,7 @@ def load(path: str | None = None):
             f"{p} not found. Build it with `python psana-ray_b200/build.py` (needs nvcc; sm_100a). "
             "This package has no CPU fallback.")
     try:
-        lib = C.CDLL(p, mode=C.RTLD_GLOBAL)
+        lib = C.CDLL(p)        # RTLD_LOCAL: several builds of the library can coexist in one process
     except OSError as e:
         raise NativeLibraryError(f"cannot load {p}: {e}") from e
     for name, (res, args) in SIGNATURES.items():
