@@ -254,7 +254,6 @@ def main():
                         "frames_per_sec_per_core": fpp / walls[-1]}
 
     import torch
-    import torch.distributed as dist
     from psana_ray import synthetic as syn
     from psana_ray.calib import GpuCalibrator
 
@@ -262,12 +261,11 @@ def main():
         raise SystemExit("bench.py needs a CUDA device; there is no CPU fallback (use --impl reference for the CPU arm)")
     dev = local_rank % torch.cuda.device_count()
     torch.cuda.set_device(dev)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", dev))
+    from psana_ray import dist_util as du
+    du.init("nccl", device=torch.device("cuda", dev))
 
     def barrier():
-        if world > 1:
-            dist.barrier()
+        du.barrier()
         torch.cuda.synchronize()
 
     spec = syn.detector_spec(detector)
@@ -319,11 +317,8 @@ def main():
             torch.cuda.synchronize()
     sampler.stop()
     clocks = sampler.summary(t_wall0, t_wall1)
-    t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms_max = float(t.item())
-    value = world * B * args.steps / (total_ms_max / 1e3)
+    total_ms_max = du.max_over_ranks(total_ms, device="cuda")
+    value = du.whole_job_throughput(B * args.steps, world, total_ms_max / 1e3)
 
     # ---- end to end through the C ABI from HOST buffers ---------------------------------------------------
     # The product path (what the producer does per batch): pinned host raw -> H2D in chunks on a side stream ->
@@ -344,10 +339,7 @@ def main():
             fn()
         barrier()
         # the calls block on the library's own streams, so the host clock brackets the device work
-        t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return world * B * n / float(t.item())
+        return du.whole_job_throughput(B * n, world, du.max_over_ranks(time.perf_counter() - t0, device="cuda"))
 
     for _ in range(3):
         e2e_step()
@@ -393,8 +385,7 @@ def main():
             "clocks": clocks,
         }
         print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    du.finalize()
     return 0
 
 

@@ -1,0 +1,57 @@
+"""Multi-rank plumbing for the measurement harness: one process per GPU, events sharded by rank
+exactly as the MPI producer shards them (ref: psana_ray/producer.py:138-140 + psana MPIDataSource),
+NO collective on the data path.  torch.distributed is used for the barrier around the timed region
+and for the max-over-ranks of the timing only (backend nccl on GPUs, gloo on CPU)."""
+from __future__ import annotations
+
+import os
+
+
+def env_world():
+    return int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+
+
+def init(backend: str, device=None):
+    import torch.distributed as dist
+    rank, world, _ = env_world()
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        if device is not None:
+            dist.init_process_group(backend, device_id=device)
+        else:
+            dist.init_process_group(backend)
+    return rank, world
+
+
+def barrier():
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        dist.barrier()
+
+
+def max_over_ranks(seconds: float, device="cpu") -> float:
+    """Slowest rank's time: the job is done when the last rank is."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        return float(seconds)
+    t = torch.tensor([seconds], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def shard(nevents: int, rank: int, size: int):
+    """Event numbers of one rank: nevent % size == rank."""
+    return range(rank, nevents, size)
+
+
+def whole_job_throughput(units_per_rank: int, world: int, seconds_max: float) -> float:
+    """Weak scaling: every rank processed units_per_rank units; value = all units / slowest rank's time."""
+    return world * units_per_rank / seconds_max
+
+
+def finalize():
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        dist.destroy_process_group()
