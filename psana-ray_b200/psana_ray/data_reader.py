@@ -66,10 +66,17 @@ class DataReader:
         """The rest of the current batch (or the next one) as ``[rank, idx0, data(n, ...), photon_energies]``; None if empty."""
         if self._queue is None:
             raise RuntimeError("DataReader is not connected. Call connect() first.")
-        if self._batch is None and not self._fetch():
-            return None
+        if self._batch is not None and self._cursor >= self._batch.count:
+            self._finish_batch()                      # hands the slab back to its producer
         if self._batch is None:
-            return None
+            if not self._fetch():
+                return None
+            if self._pending_sentinel:
+                self._pending_sentinel = False
+                return None
+            if self._loose is not None:               # a plain per-event item: a batch of one
+                item, self._loose = self._loose, None
+                return item
         b, c = self._batch, self._cursor
         out = [b.rank, b.idx0 + c, self._tensor[c:], list(b.photon_energy[c:])]
         self._cursor = b.count

@@ -79,6 +79,44 @@ class SyntheticSource:
     def event_numbers(self):
         return list(range(self.rank, self.num_events, self.size))
 
+    # -- batch fast path (throughput runs) --------------------------------------------------------------------
+    def iter_raw_batches(self, batch_size, pinned=True):
+        """Yields ``(raw (n, nseg, rows, cols) uint16, photon_energies, first_local_index)`` with zero per-event
+        host work: the rank's local event i is frame ``i % P`` of a pool of P = 2 * batch_size frames held in
+        pinned memory, so a batch is a contiguous view that the H2D copy reads directly.  (The per-event
+        ``iter_raw_events`` stays the reference-shaped path; this one exists so that a throughput measurement
+        is limited by PCIe and the GPU, not by NumPy in the source.)"""
+        P = 2 * batch_size
+        reps = -(-P // self._pool.shape[0])
+        pool = np.concatenate([self._pool] * reps)[:P]
+        p0 = self._pool.shape[0]
+        if P > p0:                                   # make the repeated frames differ in their ADC bits
+            pool[p0:] ^= (np.arange(P - p0, dtype=np.uint16) % 257 + 1)[:, None, None, None]
+        holder = None
+        if pinned:
+            try:
+                import torch
+                holder = torch.from_numpy(pool.view(np.int16)).pin_memory()
+                pool = holder.numpy().view(np.uint16)
+            except Exception:
+                holder = None
+        self._batch_pool = (pool, holder)
+        nlocal = len(range(self.rank, self.num_events, self.size))
+        i = 0
+        while i < nlocal:
+            n = min(batch_size, nlocal - i)
+            off = i % P
+            if off + n > P:
+                n = P - off
+            energies = [self.photon_energy(self.rank + (i + k) * self.size) for k in range(n)]
+            yield pool[off:off + n], energies, i
+            i += n
+
+    def batch_pool_frame(self, local_index):
+        """Frame served for local event ``local_index`` by iter_raw_batches (for checks)."""
+        pool, _ = self._batch_pool
+        return pool[local_index % pool.shape[0]]
+
 
 class PsanaSource:
     """psana-backed source (LCLS-I psana1).  Needs ``import psana``; raises ImportError otherwise."""

@@ -56,6 +56,8 @@ def parse_arguments(argv=None):
     parser.add_argument("--reliable_sentinels", action="store_true",
                         help="Retry the end-of-stream sentinels with the put back-off instead of dropping them when the queue is full "
                              "(the reference drops them: producer.py:125 ignores put's result)")
+    parser.add_argument("--batch_source", action="store_true",
+                        help="Synthetic source only: serve whole batches from a pinned pool (no per-event host work); for throughput runs")
     parser.add_argument("--device", type=int, default=None, help="CUDA device (default: local rank %% device count)")
     return parser.parse_args(argv)
 
@@ -210,6 +212,18 @@ class GpuBatchPipeline:
         self.cal.calib_host(self.h_raw[:n], d_out=d_out, image=self.image)     # returns when the slab is final
         return self.ring.ref(i, n), lease
 
+    def process_view(self, h_raw_view, queue):
+        """As process(), for n frames already contiguous in (pinned) host memory: no staging copy."""
+        n = h_raw_view.shape[0]
+        self.poll(queue)
+        got = self.ring.acquire()
+        if got is None:
+            return None
+        i, slab, lease = got
+        d_out = slab[:n].view((n,) + (self.cal.image_shape if self.image else self.spec.shape))
+        self.cal.calib_host(h_raw_view, d_out=d_out, image=self.image)
+        return self.ring.ref(i, n), lease
+
     def unprocess(self, lease):
         self.ring.give_back(lease)
 
@@ -243,7 +257,35 @@ def _backoff_put(queue, item, weight, lease, rank, what):
             time.sleep(1)
 
 
-def produce_data(source, pipeline, queue, world, num_consumers=1, max_steps=None, sleep=time.sleep, reliable_sentinels=False):
+def produce_batches(source, pipeline, queue, world, max_steps=None, sleep=time.sleep):
+    """Batch fast path of the event loop: the source hands out whole batches in pinned memory.  Same items,
+    same per-rank index, same back-off as produce_data; returns False if the queue died."""
+    rank = world.rank
+    for raw, energies, idx0 in source.iter_raw_batches(pipeline.batch_size):
+        n = raw.shape[0]
+        if max_steps is not None:
+            if idx0 >= max_steps:
+                break
+            if idx0 + n > max_steps:
+                n = max_steps - idx0
+                raw, energies = raw[:n], energies[:n]
+        waits = 0
+        while True:
+            res = pipeline.process_view(raw, queue)
+            if res is not None:
+                break
+            sleep(min(0.05, 0.0005 * (2 ** waits)))
+            waits = min(waits + 1, 8)
+        payload, lease = res
+        item = EventBatch(rank=rank, idx0=idx0, count=n, data=payload, photon_energy=list(energies), lease=lease)
+        if not _backoff_put(queue, item, n, lease, rank, f"idx={idx0}..{idx0 + n - 1}"):
+            return False
+        logging.debug(f"Rank {rank} produced: idx={idx0}..{idx0 + n - 1}")
+    return True
+
+
+def produce_data(source, pipeline, queue, world, num_consumers=1, max_steps=None, sleep=time.sleep, reliable_sentinels=False,
+                 batch_source=False):
     """The reference's ``produce_data`` (ref: producer.py:78-130) with events grouped into batches.
 
     ``pipeline`` needs ``batch_size``, ``stage(k, raw)``, ``process(n, queue) -> (payload, lease) | None``."""
@@ -272,7 +314,10 @@ def produce_data(source, pipeline, queue, world, num_consumers=1, max_steps=None
         return ok
 
     alive = True
-    for idx, (raw, photon_energy) in enumerate(source.iter_raw_events()):
+    if batch_source:
+        if not produce_batches(source, pipeline, queue, world, max_steps, sleep):
+            return
+    for idx, (raw, photon_energy) in enumerate(source.iter_raw_events() if not batch_source else ()):
         if max_steps is not None and idx >= max_steps:
             logging.info(f"Rank {rank}: Reached max_steps {max_steps}, terminating")
             break
@@ -351,7 +396,7 @@ def main(argv=None):
         nslabs = max(2, -(-args.queue_size // args.batch_size)) + 2
         pipeline = GpuBatchPipeline(source, psana_mode, device, args.batch_size, nslabs, bad, manual)
         produce_data(source, pipeline, queue, world, args.num_consumers, args.max_steps,
-                     reliable_sentinels=args.reliable_sentinels)
+                     reliable_sentinels=args.reliable_sentinels, batch_source=args.batch_source)
     except Exception as e:
         logging.error(f"Rank {rank}: Unhandled exception in main: {e}")
         logging.error("Traceback:")

@@ -159,6 +159,25 @@ def test_datareader_debatches_in_order_and_releases(qroot):
     assert h.poll_released("o") == [("o", 1, 1)]
 
 
+def test_read_batch_walks_batches_and_releases(qroot):
+    root, made = qroot
+    h = _mk(made, queue_name="shared_queue", ray_namespace="my", maxsize=100)
+    for k in range(3):
+        h.put(EventBatch(0, 4 * k, 4, np.full((4, 1, 2, 2), k, np.float32), [float(k)] * 4, lease=("o", k, 1)), weight=4, lease=("o", k, 1))
+    h.put(None)
+    with DataReader() as rd:
+        got = []
+        while True:
+            b = rd.read_batch()
+            if b is None:
+                assert rd.end_of_stream
+                break
+            got.append((b[1], b[2].shape[0], float(b[2].mean())))
+        assert got == [(0, 4, 0.0), (4, 4, 1.0), (8, 4, 2.0)]
+        assert sorted(h.poll_released("o")) == [("o", 0, 1), ("o", 1, 1), ("o", 2, 1)]
+        assert rd.read_batch() is None
+
+
 def test_datareader_iter_stops_at_sentinel(qroot):
     root, made = qroot
     h = _mk(made, queue_name="shared_queue", ray_namespace="my", maxsize=100)
@@ -329,3 +348,25 @@ def test_initialize_queue_get_or_create_and_failure(qroot):
     assert q2.stats()["maxsize"] == 7 and q2.stats()["pid"] == q.stats()["pid"]
     # a non-zero rank that never finds the queue gives up after max_retries and returns None (:56-71)
     assert P.initialize_queue("auto", "nowhere", "my", 7, P.World(1, 2, 1), max_retries=2, retry_delay=0.01) is None
+
+
+def test_batch_source_fast_path_same_items(qroot):
+    """--batch_source: whole batches served from a pool, no per-event host work; items keep the reference layout."""
+    root, made = qroot
+    h = _mk(made, queue_name="my", ray_namespace="default", maxsize=400)
+    src = SyntheticSource("exp", 3, "epix10k2M", rank=1, size=2, num_events=21, nseg=1)      # 10 local events
+
+    class ViewPipeline(OraclePipeline):
+        def process_view(self, raw, queue):
+            self.calls.append(raw.shape[0])
+            return np.stack([self.one(raw[k]) for k in range(raw.shape[0])]), None
+
+    pipe = ViewPipeline(src, ImageRetrievalMode.calib, batch_size=4)
+    P.produce_data(src, pipe, h, P.World(1, 1, 1), num_consumers=1, batch_source=True, max_steps=9)
+    assert sum(pipe.calls) == 9 and max(pipe.calls) <= 4
+    with DataReader(queue_name="my", ray_namespace="default") as rd:
+        items = _drain(rd)
+    assert [(i[0], i[1]) for i in items] == [(1, k) for k in range(9)]
+    for k, it in enumerate(items):
+        assert it[3] == src.photon_energy(1 + 2 * k)
+        kat.assert_same_bits(it[2], pipe.one(src.batch_pool_frame(k)))
