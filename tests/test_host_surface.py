@@ -370,3 +370,20 @@ def test_batch_source_fast_path_same_items(qroot):
     for k, it in enumerate(items):
         assert it[3] == src.photon_energy(1 + 2 * k)
         kat.assert_same_bits(it[2], pipe.one(src.batch_pool_frame(k)))
+
+
+def test_iterable_dataset_yields_whole_batches(qroot):
+    import torch
+    from torch.utils.data import DataLoader
+    from psana_ray.dataset import PsanaRayDataset
+    root, made = qroot
+    h = _mk(made, queue_name="shared_queue", ray_namespace="my", maxsize=100)
+    for k in range(3):
+        h.put(EventBatch(k % 2, 5 * k, 5, np.full((5, 2, 3, 3), k, np.float32), [1.0] * 5, lease=("o", k, 1)), weight=5, lease=("o", k, 1))
+    h.put(None)
+    seen = []
+    for data, rank, idx0, energies in DataLoader(PsanaRayDataset(), batch_size=None):
+        assert isinstance(data, torch.Tensor) and tuple(data.shape) == (5, 2, 3, 3) and len(energies) == 5
+        seen.append((int(rank), int(idx0), float(data.mean())))
+    assert seen == [(0, 0, 0.0), (1, 5, 1.0), (0, 10, 2.0)]
+    assert len(h.poll_released("o")) == 3
