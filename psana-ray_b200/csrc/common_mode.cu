@@ -122,10 +122,17 @@ __device__ __forceinline__ void block_kth_pass(const uint32_t (&key)[NKEY], uint
 #pragma unroll
     for (int i = 0; i < NKEY; ++i) {
         uint32_t m = (elig >> i) & 1u;
+        // shifts as multiply-high / multiply-add: those issue on the FMA pipe, the ALU pipe (LOP3/SHF/ISETP) is the busy one
+#if PSR_CM_UMULHI
+        if (PASS > 0) m &= (__umulhi(key[i], 1u << (32 - HSHIFT)) == prefix) ? 1u : 0u;
+        const uint32_t digit = PASS == 0 ? __umulhi(key[i], 1u << 11) : ((key[i] >> SHIFT) & DMASK);
+#else
         if (PASS > 0) m &= ((key[i] >> HSHIFT) == prefix) ? 1u : 0u;
+        const uint32_t digit = (key[i] >> SHIFT) & DMASK;
+#endif
         // predicated shared-memory reduction: no branch around the atomic
         asm volatile("{ .reg .pred q; setp.ne.u32 q, %1, 0; @q red.shared.add.u32 [%0], 1; }"
-                     :: "r"(haddr + (((key[i] >> SHIFT) & DMASK) << 2)), "r"(m) : "memory");
+                     :: "r"(digit * 4u + haddr), "r"(m) : "memory");
     }
     __syncthreads();
     uint32_t b[BPT]; uint32_t s = 0;
@@ -177,6 +184,12 @@ __device__ __forceinline__ uint32_t block_kth(const uint32_t (&key)[NKEY], uint3
 // 11-bit pass over the list, then the (typically < 32) survivors are ranked by one warp, which yields
 // both middle order statistics at once.  Anything unusual (list overflow, many survivors, the upper
 // middle value outside the survivors) falls back to the register passes -- same exact answer.
+#ifndef PSR_CM_UMULHI
+#define PSR_CM_UMULHI 0
+#endif
+#ifndef PSR_CM_BALLOT
+#define PSR_CM_BALLOT 0
+#endif
 constexpr int LISTCAP = 1024;
 
 template <int NT, int NK, int NW>
@@ -194,6 +207,7 @@ __device__ __forceinline__ void block_median_keys(const uint32_t (&key)[NK], uin
     bool have_lo = false, have_hi = false;
     uint32_t lo = 0, hi = 0;
     if (M <= LISTCAP) {                                         // uniform
+#if PSR_CM_BALLOT
         // warp-aggregated append: one shared atomic per warp per step instead of one per matching key
 #pragma unroll
         for (int i = 0; i < NK; ++i) {
@@ -206,6 +220,11 @@ __device__ __forceinline__ void block_median_keys(const uint32_t (&key)[NK], uin
                 if (hit) list[base + __popc(bal & ((1u << lane) - 1u))] = key[i];
             }
         }
+#else
+#pragma unroll
+        for (int i = 0; i < NK; ++i)
+            if (((elig >> i) & 1u) && (key[i] >> 21) == prefix) list[atomicAdd(&sh[35], 1)] = key[i];
+#endif
         __syncthreads();
         // pass 1 over the list: bits 20..10
         const uint32_t haddr = (uint32_t)__cvta_generic_to_shared(hist);
