@@ -1,48 +1,53 @@
-"""Consumer example, the counterpart of the reference's examples/psana_consumer.py (ref: :1-55).
+"""Consumer example -- what the reference's examples/psana_consumer.py does (ref: :28-47), written
+against this package's additions.
 
-Launch the producer ranks (one per GPU; ranks come from mpirun or from RANK/WORLD_SIZE):
+    # producers, one rank per GPU (ranks from mpirun or RANK/WORLD_SIZE); rank 0 starts the queue server
     mpirun -n 4 psana-ray-producer --exp mfxl1038923 --run 58 --detector_name epix10k2M --queue_size 400
-Launch a consumer on the same box:
-    python psana_consumer.py 1
+    # any number of consumers on the same box
+    python examples/psana_consumer.py --id 1
 
-Differences from the reference example: no Ray head to start (the producer's rank 0 starts the queue
-server); the queue name/namespace are passed explicitly because the reference's defaults do not match
-each other (producer: 'my'/'default', DataReader: 'shared_queue'/'my' -- ref: producer.py:26-27 vs
-data_reader.py:5); an item is unpacked into its FOUR fields (the reference unpacks three and therefore
-never processes a frame, ref: examples/psana_consumer.py:35 vs producer.py:101); `data` is a CUDA tensor.
+Notes for users of the reference example:
+  * there is no Ray head to start;
+  * pass the producer's queue name and namespace ('my' / 'default'): the reference's own defaults
+    do not agree with each other (ref: producer.py:26-27 vs data_reader.py:5);
+  * an item has FOUR fields -- the reference example unpacks three and so never gets to a frame
+    (ref: examples/psana_consumer.py:35 vs producer.py:101);
+  * `data` is a float32 CUDA tensor mapped straight from the producer's GPU memory;
+  * iterating a DataReader ends at the producer's end-of-stream sentinel, so no sleep-and-poll loop.
 """
-import signal
-import sys
-import time
+import argparse
 
 from psana_ray.data_reader import DataReader, DataReaderError
 
 
-def signal_handler(sig, frame):
-    print("Ctrl+C pressed. Shutting down...")
-    sys.exit(0)
-
-
-def consume_data(consumer_id, queue_name="my", ray_namespace="default"):
-    with DataReader(queue_name=queue_name, ray_namespace=ray_namespace) as reader:
-        while True:
-            try:
-                result = reader.read()
-                if result is not None:
-                    rank, idx, data, photon_energy = result
-                    print(f"Consumer {consumer_id} processed: rank={rank} | idx={idx} | shape={tuple(data.shape)} | device={data.device}")
-                elif reader.end_of_stream:
-                    print(f"Consumer {consumer_id}: end of stream")
-                    break
-                else:
-                    print(f"Consumer {consumer_id} waiting for data...")
-                    time.sleep(1)
-            except DataReaderError as e:
-                print(f"DataReader error: {e}")
-                print("Queue actor is dead. Exiting...")
-                break
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--id", default="1")
+    ap.add_argument("--queue_name", default="my")
+    ap.add_argument("--ray_namespace", default="default")
+    ap.add_argument("--batches", action="store_true", help="take whole GPU batches instead of single events")
+    a = ap.parse_args()
+    nevents = 0
+    try:
+        with DataReader(queue_name=a.queue_name, ray_namespace=a.ray_namespace) as reader:
+            if a.batches:
+                while not reader.end_of_stream:
+                    batch = reader.read_batch()
+                    if batch is None:
+                        continue
+                    rank, idx0, data, energies = batch
+                    nevents += data.shape[0]
+                    print(f"consumer {a.id}: rank {rank} events {idx0}..{idx0 + data.shape[0] - 1} {tuple(data.shape)} on {data.device}")
+            else:
+                for rank, idx, data, photon_energy in reader:
+                    nevents += 1
+                    print(f"consumer {a.id}: rank {rank} event {idx} {tuple(data.shape)} E={photon_energy} sum={float(data.sum()):.1f}")
+    except DataReaderError as err:
+        print(f"consumer {a.id}: the queue is gone ({err})")
+    except KeyboardInterrupt:
+        pass
+    print(f"consumer {a.id}: {nevents} events")
 
 
 if __name__ == "__main__":
-    signal.signal(signal.SIGINT, signal_handler)
-    consume_data(sys.argv[1] if len(sys.argv) > 1 else 1)
+    main()
