@@ -273,52 +273,138 @@ __device__ __forceinline__ void img_store(float* __restrict__ img, size_t off, i
     else { for (int i = 0; i < ncol; ++i) __stcs(img + off + i, v[i]); }
 }
 
+// +1: src[0..3] ascending, contiguous, src[0] % 4 == 0; -1: descending with src[3] % 4 == 0; 0: anything else.
+// npix % 4 == 0, so a run that is aligned within a frame is aligned in every frame.
+__device__ __forceinline__ int src_run(const int (&src)[4], int npix) {
+    if (src[0] >= 0 && (src[0] & 3) == 0 && src[1] == src[0] + 1 && src[2] == src[0] + 2 && src[3] == src[0] + 3 && src[3] < npix) return 1;
+    if (src[3] >= 0 && (src[3] & 3) == 0 && src[2] == src[3] + 1 && src[1] == src[3] + 2 && src[0] == src[3] + 3 && src[0] < npix) return -1;
+    return 0;
+}
+
+// Tile bookkeeping shared by the two image kernels.  A CTA owns a 64 x 16 output tile; every thread STORES
+// 4 consecutive pixels of one output row (coalesced 16-byte stores).  Which pixels a thread LOADS depends on
+// the tile: on unrotated / 180-degree panels consecutive output x are consecutive detector pixels, so a thread
+// loads what it stores; on panels rotated by 90 / 270 degrees consecutive output y are consecutive detector
+// pixels, so the tile is walked column-wise for the loads (4 consecutive y per thread = one vector load) and
+// transposed through shared memory.  The CTA votes once which way its tile goes.
+constexpr int IMG_TS = IMG_TW + 1;                     // padded shared row stride
+
+struct ImgTile {
+    int x0, y, ncol; bool store_ok; size_t p0;         // store role
+    int src[4]; int run; bool transposed; int tx, ty0; // load role
+};
+
+__device__ __forceinline__ int inv_at(const int32_t* __restrict__ inv, const uint8_t* __restrict__ keep, int H, int W, int y, int x) {
+    if (y >= H || x >= W) return -1;
+    const size_t p = (size_t)y * W + x;
+    if (keep != nullptr && !__ldg(keep + p)) return -1;
+    return __ldg(inv + p);
+}
+
+__device__ __forceinline__ void img_tile_setup(ImgTile& t, const int32_t* __restrict__ inv, const uint8_t* __restrict__ keep,
+                                               int H, int W, int npix) {
+    const int tid = threadIdx.x;
+    const int bx = blockIdx.x * IMG_TW, by = blockIdx.y * IMG_TH;
+    t.x0 = bx + (tid & 15) * 4; t.y = by + (tid >> 4);
+    t.store_ok = t.y < H && t.x0 < W;
+    t.ncol = t.store_ok ? min(4, W - t.x0) : 0;
+    t.p0 = (size_t)t.y * W + t.x0;
+    int rowsrc[4], colsrc[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) rowsrc[i] = inv_at(inv, keep, H, W, t.y, t.x0 + i);
+    t.tx = tid >> 2; t.ty0 = (tid & 3) * 4;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) colsrc[i] = inv_at(inv, keep, H, W, by + t.ty0 + i, bx + t.tx);
+    const int rrun = src_run(rowsrc, npix), crun = src_run(colsrc, npix);
+    const int nrow = __syncthreads_count(rrun != 0), ncolv = __syncthreads_count(crun != 0);
+    t.transposed = ncolv > nrow;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) t.src[i] = t.transposed ? colsrc[i] : rowsrc[i];
+    t.run = t.transposed ? crun : rrun;
+}
+
+// v[u][0..3] = this thread's LOADED values of frames f0+u (u < nf) -> image, through shared memory when the
+// tile is transposed (all frames of the group share two barriers)
+#ifndef PSR_IMG_NU
+#define PSR_IMG_NU 1
+#endif
+constexpr int IMG_NU = PSR_IMG_NU;                              // frames per group: loads of the whole group are in flight together
+
+template <bool VEC>
+__device__ __forceinline__ void img_tile_store(const ImgTile& t, float* __restrict__ tilebuf, float* __restrict__ img,
+                                               size_t fimg, int f0, int nf, const float (&v)[IMG_NU][4]) {
+    if (!t.transposed) {
+        if (t.store_ok) {
+#pragma unroll
+            for (int u = 0; u < IMG_NU; ++u)
+                if (u < nf) img_store<VEC>(img, (size_t)(f0 + u) * fimg + t.p0, t.ncol, v[u]);
+        }
+        return;
+    }
+#pragma unroll
+    for (int u = 0; u < IMG_NU; ++u)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) tilebuf[u * (IMG_TH * IMG_TS) + (t.ty0 + i) * IMG_TS + t.tx] = v[u][i];
+    __syncthreads();
+    if (t.store_ok) {
+        const int r = threadIdx.x >> 4, cx = (threadIdx.x & 15) * 4;
+#pragma unroll
+        for (int u = 0; u < IMG_NU; ++u) {
+            if (u < nf) {
+                const float* tb = tilebuf + u * (IMG_TH * IMG_TS) + r * IMG_TS + cx;
+                const float w[4] = {tb[0], tb[1], tb[2], tb[3]};
+                img_store<VEC>(img, (size_t)(f0 + u) * fimg + t.p0, t.ncol, w);
+            }
+        }
+    }
+    __syncthreads();
+}
+
 // from an already calibrated batch (common mode on): out[f][p] = src < 0 ? 0 : calib[f][src]
 template <bool VEC>
 __global__ void __launch_bounds__(256)
 image_gather_kernel(const float* __restrict__ calib, float* __restrict__ img, const int32_t* __restrict__ inv,
                     const uint8_t* __restrict__ keep, int H, int W, int npix, int nframes)
 {
-    const int x0 = blockIdx.x * IMG_TW + (threadIdx.x & 15) * 4;
-    const int y = blockIdx.y * IMG_TH + (threadIdx.x >> 4);
-    if (y >= H || x0 >= W) return;
-    const int ncol = min(4, W - x0);
-    const size_t p0 = (size_t)y * W + x0;
-    int src[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        src[i] = (i < ncol) ? __ldg(inv + p0 + i) : -1;
-        if (keep != nullptr && i < ncol && !__ldg(keep + p0 + i)) src[i] = -1;
-    }
+    __shared__ float tilebuf[IMG_NU * IMG_TH * IMG_TS];
+    ImgTile t;
+    img_tile_setup(t, inv, keep, H, W, npix);
     const size_t fimg = (size_t)H * W;
-    for (int f = blockIdx.z; f < nframes; f += gridDim.z) {
-        float v[4];
+    // blockIdx.z owns a contiguous range of frames, walked in groups of IMG_NU
+    const int per = (nframes + gridDim.z - 1) / gridDim.z;
+    const int f_begin = blockIdx.z * per, f_end = min(nframes, f_begin + per);
+    for (int f0 = f_begin; f0 < f_end; f0 += IMG_NU) {
+        const int nf = min(IMG_NU, f_end - f0);
+        float v[IMG_NU][4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) v[i] = src[i] >= 0 ? __ldg(calib + (size_t)f * npix + src[i]) : 0.0f;
-        img_store<VEC>(img, (size_t)f * fimg + p0, ncol, v);
+        for (int u = 0; u < IMG_NU; ++u) {
+            const float* cf = calib + (size_t)(f0 + (u < nf ? u : 0)) * npix;
+            if (t.run > 0)      { const float4 q = __ldg(reinterpret_cast<const float4*>(cf + t.src[0])); v[u][0] = q.x; v[u][1] = q.y; v[u][2] = q.z; v[u][3] = q.w; }
+            else if (t.run < 0) { const float4 q = __ldg(reinterpret_cast<const float4*>(cf + t.src[3])); v[u][0] = q.w; v[u][1] = q.z; v[u][2] = q.y; v[u][3] = q.x; }
+            else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) v[u][i] = t.src[i] >= 0 ? __ldg(cf + t.src[i]) : 0.0f;
+            }
+        }
+        img_tile_store<VEC>(t, tilebuf, img, fimg, f0, nf, v);
     }
 }
 
-// fused raw -> image (no common mode): constants gathered once per output pixel, frames inner
+// fused raw -> image (no common mode): constants gathered once per loaded pixel, frames inner
 template <int DET, bool HAS_OFFS, bool VEC>
 __global__ void __launch_bounds__(256)
 image_fused_kernel(const uint16_t* __restrict__ raw, float* __restrict__ img, PsrDev c, int nframes, int fpb)
 {
-    const int x0 = blockIdx.x * IMG_TW + (threadIdx.x & 15) * 4;
-    const int y = blockIdx.y * IMG_TH + (threadIdx.x >> 4);
-    if (y >= c.H || x0 >= c.W) return;
-    const int ncol = min(4, c.W - x0);
-    const size_t p0 = (size_t)y * c.W + x0;
+    __shared__ float tilebuf[IMG_NU * IMG_TH * IMG_TS];
+    ImgTile t;
+    img_tile_setup(t, c.inv, c.keep_image, c.H, c.W, c.npix);
     const int f_begin = blockIdx.z * fpb;
     const int f_end = min(nframes, f_begin + fpb);
-    int src[4]; uint32_t fl[4];
+    uint32_t fl[4];
     float A[4][3], B[4][3], G[4][3];   // epix: A = {ped0, ped1}, G = {gf0, gf1}; jungfrau: A peds, B offs, G gfac
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        int s = (i < ncol) ? __ldg(c.inv + p0 + i) : -1;
-        if (c.keep_image != nullptr && i < ncol && !__ldg(c.keep_image + p0 + i)) s = -1;
-        src[i] = s;
-        const int q = s < 0 ? 0 : s;
+        const int q = t.src[i] < 0 ? 0 : t.src[i];
         fl[i] = __ldg(c.flags + q) | PSR_FL_KEEP;     // calib-layout keep mask does not apply to images
         if (DET == 0) {
             A[i][0] = __ldg(c.ped0 + q); A[i][1] = __ldg(c.ped1 + q); A[i][2] = 0.f;
@@ -334,20 +420,30 @@ image_fused_kernel(const uint16_t* __restrict__ raw, float* __restrict__ img, Ps
         }
     }
     const size_t fimg = (size_t)c.H * c.W;
-    for (int f = f_begin; f < f_end; ++f) {
-        const uint16_t* rf = raw + (size_t)f * c.npix;
-        uint32_t r[4];
+    for (int f0 = f_begin; f0 < f_end; f0 += IMG_NU) {
+        const int nf = min(IMG_NU, f_end - f0);
+        uint32_t r[IMG_NU][4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) r[i] = src[i] >= 0 ? (uint32_t)__ldg(rf + src[i]) : 0u;
-        float v[4];
+        for (int u = 0; u < IMG_NU; ++u) {
+            const uint16_t* rf = raw + (size_t)(f0 + (u < nf ? u : 0)) * c.npix;
+            if (t.run > 0)      { const uint2 q = __ldg(reinterpret_cast<const uint2*>(rf + t.src[0])); r[u][0] = q.x & 0xFFFFu; r[u][1] = q.x >> 16; r[u][2] = q.y & 0xFFFFu; r[u][3] = q.y >> 16; }
+            else if (t.run < 0) { const uint2 q = __ldg(reinterpret_cast<const uint2*>(rf + t.src[3])); r[u][3] = q.x & 0xFFFFu; r[u][2] = q.x >> 16; r[u][1] = q.y & 0xFFFFu; r[u][0] = q.y >> 16; }
+            else {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            float o;
-            if (DET == 0) o = epix_px(r[i], A[i][0], G[i][0], A[i][1], G[i][1], fl[i]);
-            else          o = jf_px<HAS_OFFS>(r[i], A[i], B[i], G[i], fl[i]);
-            v[i] = src[i] >= 0 ? o : 0.0f;
+                for (int i = 0; i < 4; ++i) r[u][i] = t.src[i] >= 0 ? (uint32_t)__ldg(rf + t.src[i]) : 0u;
+            }
         }
-        img_store<VEC>(img, (size_t)f * fimg + p0, ncol, v);
+        float v[IMG_NU][4];
+#pragma unroll
+        for (int u = 0; u < IMG_NU; ++u)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                float o;
+                if (DET == 0) o = epix_px(r[u][i], A[i][0], G[i][0], A[i][1], G[i][1], fl[i]);
+                else          o = jf_px<HAS_OFFS>(r[u][i], A[i], B[i], G[i], fl[i]);
+                v[u][i] = t.src[i] >= 0 ? o : 0.0f;
+            }
+        img_tile_store<VEC>(t, tilebuf, img, fimg, f0, nf, v);
     }
 }
 
