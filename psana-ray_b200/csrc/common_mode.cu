@@ -583,7 +583,11 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     float cm = 0.f; bool apply = false;
     if (n >= c.npix_min && n > 0) {                        // uniform across the CTA
         uint32_t lo, hi;
+#ifdef PSR_CM_SKIPSEL      /* timing experiment only: wrong results */
+        lo = hi = key[0];
+#else
         block_median_keys<NT, NK, NW>(key, elig, n, hist, selsh, list, red, lo, hi);
+#endif
         cm = psr_mid(psr_key2f(lo), psr_key2f(hi));
         apply = !(fabsf(cm) > c.cormax);
     }
