@@ -621,6 +621,114 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     }
 }
 
+// =================================================================================================
+// epix10ka, mode 4, FRAMES-INNER: a CTA owns one bank tile and walks `fpc` frames of the batch.  The
+// tile's pedestals (both bit-14 entries, 67.6 KB) and flag bytes are staged ONCE in shared memory --
+// each thread only ever reads the slots of its own 24 pixels, so no barrier guards them -- which
+// removes most of the per-frame constant traffic from L2 that bounded the one-frame-per-CTA kernel
+// (profiles/README.md: 394 of 702 us).  The gain factors of the epilogue still come from L2.
+// =================================================================================================
+template <int NT, int MINB>
+__global__ void __launch_bounds__(NT, MINB)
+cm_banks_epix_fi_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c, int nframes, int fpc)
+{
+    constexpr int ROWS = 352, COLS = 384, NB = 8, TR = ROWS / 2, TC = COLS / NB, CH = TC / 8, NCH = TR * CH, CPT = NCH / NT, NK = CPT * 8;
+    constexpr int NW = NT / 32;
+    static_assert(NCH % NT == 0 && NT % 32 == 0 && NK <= 32, "tile must split evenly over the CTA");
+    extern __shared__ float4 sm4[];                               // [4][NCH]: ped0 px0-3, ped0 px4-7, ped1 px0-3, ped1 px4-7
+    uint2* sfl = reinterpret_cast<uint2*>(sm4 + 4 * NCH);         // [NCH] flag bytes of the chunk
+    __shared__ int redbuf[64];
+    __shared__ uint32_t hist[2048];
+    __shared__ uint32_t list[LISTCAP + 32];
+    __shared__ int selsh[40];
+
+    const int tid = threadIdx.x;
+    int bid = blockIdx.x;
+    const int bank = bid % NB; bid /= NB;
+    const int half = bid & 1;  bid >>= 1;
+    const int seg = bid;
+    const int f_begin = blockIdx.y * fpc, f_end = min(nframes, f_begin + fpc);
+    const uint32_t keep_or = c.ignore_keep ? 0x08080808u : 0u;
+
+    int gpj[CPT];
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+        const int ch = tid + j * NT;
+        const int r = ch / CH, cc = ch - r * CH;
+        const int gp = ((seg * ROWS + half * TR + r) * COLS) + bank * TC + cc * 8;
+        gpj[j] = gp;
+        sm4[0 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped0 + gp));
+        sm4[1 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped0 + gp) + 1);
+        sm4[2 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped1 + gp));
+        sm4[3 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped1 + gp) + 1);
+        uint2 f = __ldg(reinterpret_cast<const uint2*>(c.flags + gp));
+        f.x |= keep_or; f.y |= keep_or;
+        sfl[ch] = f;
+    }
+
+    BlockRed<NW> red{redbuf, 0};
+    for (int frame = f_begin; frame < f_end; ++frame) {
+        const uint16_t* rawf = raw + (size_t)frame * c.npix;
+        float* outf = out + (size_t)frame * c.npix;
+        uint32_t key[NK];
+        uint32_t elig = 0, sel0 = 0;
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+            const int ch = tid + j * NT;
+            const uint4 rv = __ldcs(reinterpret_cast<const uint4*>(rawf + gpj[j]));
+            const uint32_t w[4] = {rv.x, rv.y, rv.z, rv.w};
+            const float4 a0 = sm4[0 * NCH + ch], a1 = sm4[1 * NCH + ch], b0 = sm4[2 * NCH + ch], b1 = sm4[3 * NCH + ch];
+            const float pa[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const float pb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+            const uint2 fv = sfl[ch];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int q = j * 8 + i;
+                const uint32_t v = (i & 1) ? (w[i >> 1] >> 16) : (w[i >> 1] & 0xFFFFu);
+                const uint32_t f = (i < 4 ? fv.x : fv.y) >> (8 * (i & 3));
+                const uint32_t sel = (v >> 14) & 1u;
+                const float x = __fsub_rn((float)(v & 0x3FFFu), sel ? pb[i] : pa[i]);
+                const uint32_t el = sel ? (f & PSR_FL_ELIG1) : (f & PSR_FL_ELIG0);
+                key[q] = psr_f2key(x);
+                elig |= (el ? 1u : 0u) << q;
+                sel0 |= sel << q;
+            }
+        }
+
+        // common_mode_2d: skip if n < npix_min, skip if |cm| > cormax
+        const int n = red.sum(__popc(elig));
+        float cm = 0.f; bool apply = false;
+        if (n >= c.npix_min && n > 0) {                        // uniform across the CTA
+            uint32_t lo, hi;
+            block_median_keys<NT, NK, NW>(key, elig, n, hist, selsh, list, red, lo, hi);
+            cm = psr_mid(psr_key2f(lo), psr_key2f(hi));
+            apply = !(fabsf(cm) > c.cormax);
+        }
+
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+            const int ch = tid + j * NT;
+            const int gp = gpj[j];
+            float ga[8], gb_[8];
+            ld8(c.gf0 + gp, ga); ld8(c.gf1 + gp, gb_);
+            const uint2 fv = sfl[ch];
+            float o[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int q = j * 8 + i;
+                const uint32_t f = (i < 4 ? fv.x : fv.y) >> (8 * (i & 3));
+                float x = psr_key2f(key[q]);
+                if (apply && ((elig >> q) & 1u)) x = __fsub_rn(x, cm);
+                const float gf = ((sel0 >> q) & 1u) ? gb_[i] : ga[i];
+                const float v = __fmul_rn(__fmul_rn(x, gf), (f & PSR_FL_MASK) ? 1.0f : 0.0f);
+                o[i] = (f & PSR_FL_KEEP) ? v : 0.0f;
+            }
+            __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
+            __stcs(reinterpret_cast<float4*>(outf + gp + 4), make_float4(o[4], o[5], o[6], o[7]));
+        }
+    }
+}
+
 constexpr int EPIX_NT = 352, JF_NT = 512;
 #ifndef PSR_CMB_EPIX_NT          /* banks-only kernel: threads, min CTAs/SM, pixels per chunk */
 #define PSR_CMB_EPIX_NT 352
@@ -629,6 +737,10 @@ constexpr int EPIX_NT = 352, JF_NT = 512;
 #endif
 constexpr size_t EPIX_SMEM = (size_t)(176 * 49) * 5;     // float + flag byte per padded tile pixel
 constexpr size_t JF_SMEM = (size_t)(256 * 65) * 5;
+constexpr size_t EPIX_FI_SMEM = (size_t)1056 * (4 * 16 + 8);     // pedestals + flag bytes of one bank tile
+#ifndef PSR_CM_FPC
+#define PSR_CM_FPC 8           /* frames per CTA of the frames-inner common-mode kernel */
+#endif
 
 }  // namespace
 
@@ -636,6 +748,8 @@ cudaError_t psr_common_mode_setup(void)
 {
     cudaError_t e = cudaFuncSetAttribute(cm_calib_kernel<0, 352, 384, 8, EPIX_NT>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_SMEM);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(cm_banks_epix_fi_kernel<EPIX_NT, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_FI_SMEM);
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(cm_calib_kernel<1, 512, 1024, 16, JF_NT>,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JF_SMEM);
@@ -646,7 +760,12 @@ cudaError_t psr_launch_common_mode(const PsrDev& c, const uint16_t* d_raw, int n
     if (nframes <= 0) return cudaSuccess;
     if (c.det_kind == 0) {
         const unsigned grid = (unsigned)nframes * c.nseg * 2 * 8;
-        if (c.cm_mode == 4) cm_banks_kernel<0, 352, 384, 8, PSR_CMB_EPIX_NT, PSR_CMB_EPIX_MINB, PSR_CMB_EPIX_CW><<<grid, PSR_CMB_EPIX_NT, 0, st>>>(d_raw, d_out, c);
+        if (c.cm_mode == 4 && PSR_CM_FPC > 1 && nframes > 1) {
+            const int fpc = PSR_CM_FPC;
+            dim3 g2((unsigned)c.nseg * 2 * 8, (unsigned)((nframes + fpc - 1) / fpc));
+            cm_banks_epix_fi_kernel<EPIX_NT, 2><<<g2, EPIX_NT, EPIX_FI_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
+        }
+        else if (c.cm_mode == 4) cm_banks_kernel<0, 352, 384, 8, PSR_CMB_EPIX_NT, PSR_CMB_EPIX_MINB, PSR_CMB_EPIX_CW><<<grid, PSR_CMB_EPIX_NT, 0, st>>>(d_raw, d_out, c);
         else cm_calib_kernel<0, 352, 384, 8, EPIX_NT><<<grid, EPIX_NT, EPIX_SMEM, st>>>(d_raw, d_out, c);
     } else {
         const unsigned grid = (unsigned)nframes * c.nseg * 2 * 16;
