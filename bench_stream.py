@@ -49,7 +49,7 @@ def main():
     ap.add_argument("--consumers", type=int, default=0)
     ap.add_argument("--events-per-rank", type=int, default=2048)
     ap.add_argument("--batch", type=int, default=64)
-    ap.add_argument("--queue-size", type=int, default=400)
+    ap.add_argument("--queue-size", type=int, default=1024, help="events; 400 (the reference README) makes refused puts and their 0.1-2 s back-off dominate")
     ap.add_argument("--detector", default="epix10k2M")
     ap.add_argument("--image", action="store_true")
     ap.add_argument("--common-mode", default=None)
