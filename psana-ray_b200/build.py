@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libpsana_ray_cuda.so")
 SOURCES = ["capi.cu", "calib_map.cu", "common_mode.cu"]
-HEADERS = [os.path.join(CSRC, "psr_kernels.cuh"), os.path.join(HERE, "..", "include", "psana_ray_cuda.h")]
+HEADERS = [os.path.join(CSRC, "psr_kernels.cuh"), os.path.join(CSRC, "sortnet.cuh"), os.path.join(HERE, "..", "include", "psana_ray_cuda.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -14,6 +14,18 @@
 // no sorting and no atomics.  The 2-d median counts across the CTA (keys live in registers,
 // one barrier per step); row and column medians are done by one warp per line with shuffles.
 #include "psr_kernels.cuh"
+#include "sortnet.cuh"
+
+// experiment switches (profiles/README.md records what each one measured)
+#ifndef PSR_CM_MATCH
+#define PSR_CM_MATCH 0
+#endif
+#ifndef PSR_CM_UMULHI
+#define PSR_CM_UMULHI 0
+#endif
+#ifndef PSR_CM_BALLOT
+#define PSR_CM_BALLOT 0
+#endif
 
 namespace {
 
@@ -105,6 +117,78 @@ __device__ __forceinline__ float warp_median(const uint32_t (&key)[NK], int n) {
     return psr_mid(psr_key2f(lo), psr_key2f(hi));
 }
 
+
+// Medians of C lines (columns) held by one warp, NK keys per lane per line, by a 4 x 8-bit radix select on
+// warp-private 256-bin histograms in shared memory (wh: C * 256 words).  The C selections are independent
+// instruction streams, interleaved to hide the shared-memory round trips of each pass.  Ineligible keys are
+// KEY_INELIGIBLE; a line with n == 0 returns garbage that the caller ignores.
+template <int NK, int C>
+__device__ __forceinline__ void warp_kth_radix_multi(const uint32_t (&key)[C][NK], const int (&kin)[C], uint32_t* wh, uint32_t (&res)[C]) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t waddr = (uint32_t)__cvta_generic_to_shared(wh);
+    uint32_t prefix[C]; int k[C];
+#pragma unroll
+    for (int q = 0; q < C; ++q) { prefix[q] = 0; k[q] = kin[q]; }
+#pragma unroll
+    for (int pass = 0; pass < 4; ++pass) {
+        const int shift = 24 - 8 * pass;
+#pragma unroll
+        for (int q = 0; q < C; ++q) {
+            reinterpret_cast<uint4*>(wh + q * 256)[2 * lane] = make_uint4(0, 0, 0, 0);
+            reinterpret_cast<uint4*>(wh + q * 256)[2 * lane + 1] = make_uint4(0, 0, 0, 0);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < C; ++q)
+#pragma unroll
+            for (int i = 0; i < NK; ++i) {
+                uint32_t m = key[q][i] != KEY_INELIGIBLE ? 1u : 0u;
+                if (pass > 0) m &= ((key[q][i] >> (shift + 8)) == prefix[q]) ? 1u : 0u;
+#if PSR_CM_MATCH
+                // a column's values share their high bits, so plain atomics would hit one address 32 times:
+                // lanes with the same digit elect a leader that adds their count once
+                const uint32_t digit = m ? ((key[q][i] >> shift) & 0xFFu) : 256u;
+                const uint32_t peers = __match_any_sync(0xFFFFFFFFu, digit);
+                const uint32_t lead = (peers & (0u - peers)) == (1u << lane) ? m : 0u;
+                asm volatile("{ .reg .pred p; setp.ne.u32 p, %1, 0; @p red.shared.add.u32 [%0], %2; }"
+                             :: "r"(waddr + q * 1024 + ((digit & 0xFFu) << 2)), "r"(lead), "r"(__popc(peers)) : "memory");
+#else
+                asm volatile("{ .reg .pred p; setp.ne.u32 p, %1, 0; @p red.shared.add.u32 [%0], 1; }"
+                             :: "r"(waddr + q * 1024 + (((key[q][i] >> shift) & 0xFFu) << 2)), "r"(m) : "memory");
+#endif
+            }
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < C; ++q) {
+            const uint4 b0 = reinterpret_cast<const uint4*>(wh + q * 256)[2 * lane], b1 = reinterpret_cast<const uint4*>(wh + q * 256)[2 * lane + 1];
+            const uint32_t b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+            uint32_t s = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) s += b[j];
+            uint32_t incl = s;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+            const uint32_t excl = incl - s;
+            const bool mine = (uint32_t)k[q] >= excl && (uint32_t)k[q] < incl;
+            uint32_t bin = 0, r = 0;
+            if (mine) {
+                r = (uint32_t)k[q] - excl; bool done = false;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (!done) { if (r < b[j]) { bin = 8 * lane + j; done = true; } else r -= b[j]; }
+            }
+            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, mine);
+            const int src = bal ? __ffs(bal) - 1 : 0;
+            bin = __shfl_sync(0xFFFFFFFFu, bin, src);
+            k[q] = (int)__shfl_sync(0xFFFFFFFFu, r, src);
+            prefix[q] = (prefix[q] << 8) | bin;
+        }
+        __syncwarp();
+    }
+#pragma unroll
+    for (int q = 0; q < C; ++q) res[q] = prefix[q];
+}
+
 // ---- CTA-wide exact selection: 3-pass radix select (11 + 11 + 10 bits) on a 2048-bin shared histogram.
 // Keys stay in registers; bit i of `elig` says key[i] takes part.  Returns the k-th smallest (0-based)
 // eligible key; k must be < the number of eligible keys.  Every thread of the CTA must call it.
@@ -184,12 +268,6 @@ __device__ __forceinline__ uint32_t block_kth(const uint32_t (&key)[NKEY], uint3
 // 11-bit pass over the list, then the (typically < 32) survivors are ranked by one warp, which yields
 // both middle order statistics at once.  Anything unusual (list overflow, many survivors, the upper
 // middle value outside the survivors) falls back to the register passes -- same exact answer.
-#ifndef PSR_CM_UMULHI
-#define PSR_CM_UMULHI 0
-#endif
-#ifndef PSR_CM_BALLOT
-#define PSR_CM_BALLOT 0
-#endif
 constexpr int LISTCAP = 1024;
 
 template <int NT, int NK, int NW>
@@ -315,11 +393,13 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     extern __shared__ float smem[];
     float* a = smem;                                           // TR * ST
     uint8_t* fl = reinterpret_cast<uint8_t*>(a + TR * ST);     // TR * ST
+    // four 256-bin histograms per warp for the column medians, 16-byte aligned behind the tile
+    uint32_t* whist = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(smem) + ((TR * ST * 5 + 15) / 16) * 16);
     __shared__ int redbuf[64];
     __shared__ uint32_t hist[2048];
     __shared__ int selsh[40];
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
     int bid = blockIdx.x;
     const int bank = bid % NB; bid /= NB;
     const int half = bid & 1;  bid >>= 1;
@@ -423,25 +503,29 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     __syncthreads();
 
     // ---- mode 1: per-row medians within the bank (common_mode_rows: n > npix_min and |cm| < cormax)
+    // One THREAD per row: the row's 48 / 64 keys go into registers and through a Batcher sorting network
+    // (sortnet.cuh; ineligible pixels are +inf keys that sink to the end), ~8x fewer instructions than a
+    // warp-wide counting search per row.  Row r of the tile is read with stride ST = TC + 1: conflict-free.
     if (mode & 1) {
-        constexpr int NK = (TC + 31) / 32;
-        for (int r = warp; r < TR; r += NW) {
-            uint32_t k[NK]; int cnt = 0;
+        for (int r = tid; r < TR; r += NT) {
+            uint32_t k[TC]; int n = 0;
 #pragma unroll
-            for (int i = 0; i < NK; ++i) {
-                const int col = lane + 32 * i;
-                k[i] = KEY_INELIGIBLE;
-                if (col < TC && (fl[r * ST + col] & 2u)) { k[i] = psr_f2key(a[r * ST + col]); ++cnt; }
+            for (int col = 0; col < TC; ++col) {
+                const bool e = (fl[r * ST + col] & 2u) != 0;
+                k[col] = e ? psr_f2key(a[r * ST + col]) : KEY_INELIGIBLE;
+                n += e ? 1 : 0;
             }
-            const int n = __reduce_add_sync(0xFFFFFFFFu, cnt);
             if (n > c.npix_min && n > 0) {
-                const float cm = warp_median<NK>(k, n);
+                if (TC == 48) psr_sort48(reinterpret_cast<uint32_t (&)[48]>(k)); else psr_sort64(reinterpret_cast<uint32_t (&)[64]>(k));
+                const int k1 = (n - 1) >> 1, k2 = n >> 1;           // both <= TC / 2
+                uint32_t lo = k[0], hi = k[0];
+#pragma unroll
+                for (int i = 1; i <= TC / 2; ++i) { if (i == k1) lo = k[i]; if (i == k2) hi = k[i]; }
+                const float cm = psr_mid(psr_key2f(lo), psr_key2f(hi));
                 if (fabsf(cm) < c.cormax) {
 #pragma unroll
-                    for (int i = 0; i < NK; ++i) {
-                        const int col = lane + 32 * i;
-                        if (k[i] != KEY_INELIGIBLE) a[r * ST + col] = __fsub_rn(a[r * ST + col], cm);
-                    }
+                    for (int col = 0; col < TC; ++col)
+                        if (fl[r * ST + col] & 2u) a[r * ST + col] = __fsub_rn(a[r * ST + col], cm);
                 }
             }
         }
@@ -449,24 +533,46 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     }
 
     // ---- mode 2: per-column medians within the half (common_mode_cols: same guards)
+    // One warp takes CC columns at a time (lane = row mod 32), all CC radix selections interleaved.
     if (mode & 2) {
-        constexpr int NK = (TR + 31) / 32;
-        for (int col = warp; col < TC; col += NW) {
-            uint32_t k[NK]; int cnt = 0;
+        constexpr int NK = (TR + 31) / 32, CC = DET == 0 ? 4 : 1;      // measured: interleaving helps epix10ka, hurts jungfrau (register cap)
+        static_assert(TC % CC == 0, "columns per warp step");
+        const int warp = tid >> 5;
+        for (int col0 = warp * CC; col0 < TC; col0 += NW * CC) {
+            uint32_t k[CC][NK]; int n[CC], k1[CC];
 #pragma unroll
-            for (int i = 0; i < NK; ++i) {
-                const int r = lane + 32 * i;
-                k[i] = KEY_INELIGIBLE;
-                if (r < TR && (fl[r * ST + col] & 2u)) { k[i] = psr_f2key(a[r * ST + col]); ++cnt; }
+            for (int q = 0; q < CC; ++q) {
+                int cnt = 0;
+#pragma unroll
+                for (int i = 0; i < NK; ++i) {
+                    const int r = lane + 32 * i;
+                    k[q][i] = KEY_INELIGIBLE;
+                    if (r < TR && (fl[r * ST + col0 + q] & 2u)) { k[q][i] = psr_f2key(a[r * ST + col0 + q]); ++cnt; }
+                }
+                n[q] = __reduce_add_sync(0xFFFFFFFFu, cnt);
+                k1[q] = n[q] > 0 ? (n[q] - 1) >> 1 : 0;
             }
-            const int n = __reduce_add_sync(0xFFFFFFFFu, cnt);
-            if (n > c.npix_min && n > 0) {
-                const float cm = warp_median<NK>(k, n);
-                if (fabsf(cm) < c.cormax) {
+            uint32_t lo[CC];
+            warp_kth_radix_multi<NK, CC>(k, k1, whist + warp * (CC * 256), lo);
 #pragma unroll
-                    for (int i = 0; i < NK; ++i) {
-                        const int r = lane + 32 * i;
-                        if (k[i] != KEY_INELIGIBLE) a[r * ST + col] = __fsub_rn(a[r * ST + col], cm);
+            for (int q = 0; q < CC; ++q) {
+                if (n[q] > c.npix_min && n[q] > 0) {
+                    uint32_t hi = lo[q];
+                    if ((n[q] & 1) == 0) {                              // even count: the upper middle value
+                        int cle = 0; uint32_t mg = 0xFFFFFFFFu;
+#pragma unroll
+                        for (int i = 0; i < NK; ++i) { cle += (k[q][i] <= lo[q]); if (k[q][i] > lo[q]) mg = min(mg, k[q][i]); }
+                        cle = __reduce_add_sync(0xFFFFFFFFu, cle);
+                        mg = __reduce_min_sync(0xFFFFFFFFu, mg);
+                        if (cle <= (n[q] >> 1)) hi = mg;
+                    }
+                    const float cm = psr_mid(psr_key2f(lo[q]), psr_key2f(hi));
+                    if (fabsf(cm) < c.cormax) {
+#pragma unroll
+                        for (int i = 0; i < NK; ++i) {
+                            const int r = lane + 32 * i;
+                            if (k[q][i] != KEY_INELIGIBLE) a[r * ST + col0 + q] = __fsub_rn(a[r * ST + col0 + q], cm);
+                        }
                     }
                 }
             }
@@ -735,8 +841,8 @@ constexpr int EPIX_NT = 352, JF_NT = 512;
 #define PSR_CMB_EPIX_MINB 2
 #define PSR_CMB_EPIX_CW 8
 #endif
-constexpr size_t EPIX_SMEM = (size_t)(176 * 49) * 5;     // float + flag byte per padded tile pixel
-constexpr size_t JF_SMEM = (size_t)(256 * 65) * 5;
+constexpr size_t EPIX_SMEM = ((size_t)(176 * 49) * 5 + 15) / 16 * 16 + (EPIX_NT / 32) * 4 * 256 * 4;   // padded tile (float + flag byte) + warp histograms
+constexpr size_t JF_SMEM = ((size_t)(256 * 65) * 5 + 15) / 16 * 16 + (JF_NT / 32) * 4 * 256 * 4;
 constexpr size_t EPIX_FI_SMEM = (size_t)1056 * (4 * 16 + 8);     // pedestals + flag bytes of one bank tile
 #ifndef PSR_CM_FPC
 #define PSR_CM_FPC 8           /* frames per CTA of the frames-inner common-mode kernel */

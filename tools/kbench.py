@@ -21,9 +21,12 @@ ap.add_argument("--fpb", default="0")
 ap.add_argument("--iters", type=int, default=50)
 ap.add_argument("--batch", type=int, default=64)
 ap.add_argument("--out", default=None)
+ap.add_argument("--cm-mode", type=int, default=4)
+ap.add_argument("--det", default=None)
+ap.add_argument("--npix-min", type=int, default=10)
 a = ap.parse_args()
 
-det = "jungfrau4M" if a.workload == "jungfrau" else "epix10k2M"
+det = a.det or ("jungfrau4M" if a.workload == "jungfrau" else "epix10k2M")
 spec = syn.detector_spec(det)
 consts = syn.make_constants(spec, seed=0)
 raw = syn.make_raw_frames(spec, consts, 8, seed=1)
@@ -45,7 +48,7 @@ for path in libs:
     out_kind = 0
     nout = spec.npix
     if a.workload == "cm":
-        lib.psr_set_common_mode(ctx, 4, 100.0, 10, 0)
+        lib.psr_set_common_mode(ctx, a.cm_mode, C.c_float(100.0), a.npix_min, 0)
     if geo is not None:
         assert lib.psr_set_geometry(ctx, p(geo[0]), p(geo[1])) == 0
         H, W = C.c_int(), C.c_int(); lib.psr_image_shape(ctx, C.byref(H), C.byref(W)); nout = H.value * W.value; out_kind = 1
