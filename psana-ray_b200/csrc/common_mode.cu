@@ -8,11 +8,16 @@
 // keeps it in shared memory, runs the enabled sub-modes there and streams the result out.  HBM
 // traffic stays at raw-in + float-out; the constants of the tile come from L2.
 //
-// The median must be EXACT (NumPy: mean of the two middle order statistics, in float32).  Values
-// are mapped to order-preserving uint32 keys and the k-th smallest key is found by a most-
-// significant-bit-first search on count(key < candidate): 32 counting steps, data-independent,
-// no sorting and no atomics.  The 2-d median counts across the CTA (keys live in registers,
-// one barrier per step); row and column medians are done by one warp per line with shuffles.
+// The median must be EXACT (NumPy: mean of the two middle order statistics, in float32).  Values are
+// mapped to order-preserving uint32 keys; nothing here is approximate and nothing depends on the data:
+//   * bank (2-d) median, 8 448 / 16 384 keys per CTA: keys stay in registers, 3-pass radix select
+//     (11 + 11 + 10 bits) on a 2048-bin shared histogram with predicated red.shared, refined on a
+//     compacted candidate list and finished by one warp ranking the last <= 32 candidates;
+//   * row medians, 48 / 64 keys: one thread per row, keys in registers through a generated Batcher
+//     sorting network (sortnet.cuh);
+//   * column medians, 176 / 256 keys: one warp per column, 4 x 8-bit radix select on a warp-private
+//     histogram.
+// Guards (npix_min, cormax) and the eligible-pixels-only subtraction follow UtilsCommonMode.py.
 #include "psr_kernels.cuh"
 #include "sortnet.cuh"
 
@@ -82,41 +87,6 @@ struct BlockRed {
         return t;
     }
 };
-
-// k-th smallest (0-based) of the keys held by one warp, NK keys per lane; ineligible keys are
-// KEY_INELIGIBLE and never counted.
-template <int NK>
-__device__ __forceinline__ uint32_t warp_kth(const uint32_t (&key)[NK], int k) {
-    uint32_t prefix = 0;
-#pragma unroll 1
-    for (int bit = 31; bit >= 0; --bit) {
-        const uint32_t cand = prefix | (1u << bit);
-        int c = 0;
-#pragma unroll
-        for (int i = 0; i < NK; ++i) c += (key[i] < cand);
-        c = __reduce_add_sync(0xFFFFFFFFu, c);
-        if (c <= k) prefix = cand;
-    }
-    return prefix;
-}
-
-// median of the eligible keys of one warp (n of them, n >= 1)
-template <int NK>
-__device__ __forceinline__ float warp_median(const uint32_t (&key)[NK], int n) {
-    const int k1 = (n - 1) >> 1, k2 = n >> 1;
-    const uint32_t lo = warp_kth<NK>(key, k1);
-    uint32_t hi = lo;
-    if (k2 != k1) {
-        int cle = 0; uint32_t mg = 0xFFFFFFFFu;
-#pragma unroll
-        for (int i = 0; i < NK; ++i) { cle += (key[i] <= lo); if (key[i] > lo) mg = min(mg, key[i]); }
-        cle = __reduce_add_sync(0xFFFFFFFFu, cle);
-        mg = __reduce_min_sync(0xFFFFFFFFu, mg);
-        if (cle <= k2) hi = mg;                       // the (k2)-th is the next distinct value
-    }
-    return psr_mid(psr_key2f(lo), psr_key2f(hi));
-}
-
 
 // Medians of C lines (columns) held by one warp, NK keys per lane per line, by a 4 x 8-bit radix select on
 // warp-private 256-bin histograms in shared memory (wh: C * 256 words).  The C selections are independent
