@@ -15,8 +15,9 @@
 //     compacted candidate list and finished by one warp ranking the last <= 32 candidates;
 //   * row medians, 48 / 64 keys: one thread per row, keys in registers through a generated Batcher
 //     sorting network (sortnet.cuh);
-//   * column medians, 176 / 256 keys: one warp per column, 4 x 8-bit radix select on a warp-private
-//     histogram.
+//   * column medians, 176 / 256 keys: one warp per column, 8-bit radix select on a warp-private
+//     histogram over a linear integer image of the values (their float keys share the high bits and
+//     would all hit the same bins), ties decided by the float keys.
 // Guards (npix_min, cormax) and the eligible-pixels-only subtraction follow UtilsCommonMode.py.
 #include "psr_kernels.cuh"
 #include "sortnet.cuh"
@@ -157,6 +158,91 @@ __device__ __forceinline__ void warp_kth_radix_multi(const uint32_t (&key)[C][NK
     }
 #pragma unroll
     for (int q = 0; q < C; ++q) res[q] = prefix[q];
+}
+
+
+// k-th smallest (0-based) float key of one warp's line, selecting on a LINEAR integer image of the values.
+// A detector column's values sit in a narrow range, so their float keys share the sign/exponent bits and a
+// radix pass on those bits sends all 32 lanes to the same few histogram bins.  Instead: p = floor(x * 2^16)
+// (monotone in x), u = p - min(p) over the line, and the radix passes start at the highest bit of
+// max(u): the first digit spreads the values linearly over the 256 bins.  p is not injective; if several
+// values share the selected p the float keys of those values decide (rare: a 2^-16 ADU cell), so the
+// result is still the exact order statistic.
+template <int NK>
+__device__ __forceinline__ uint32_t warp_kth_linear(const uint32_t (&key)[NK], int k, uint32_t* wh) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t waddr = (uint32_t)__cvta_generic_to_shared(wh);
+    int p[NK]; int pmin = 0x7FFFFFFF, pmax = (int)0x80000000;
+#pragma unroll
+    for (int i = 0; i < NK; ++i) {
+        p[i] = __float2int_rd(__fmul_rn(psr_key2f(key[i]), 65536.0f));       // saturates, stays monotone
+        if (key[i] != KEY_INELIGIBLE) { pmin = min(pmin, p[i]); pmax = max(pmax, p[i]); }
+    }
+    pmin = __reduce_min_sync(0xFFFFFFFFu, pmin);
+    pmax = __reduce_max_sync(0xFFFFFFFFu, pmax);
+    uint32_t u[NK];
+#pragma unroll
+    for (int i = 0; i < NK; ++i) u[i] = key[i] != KEY_INELIGIBLE ? (uint32_t)p[i] - (uint32_t)pmin : 0xFFFFFFFFu;
+    const uint32_t range = (uint32_t)pmax - (uint32_t)pmin;
+    int s = 32 - __clz(range);                       // bits in play (0 when all values share one p); warp-uniform
+    uint32_t prefix = 0;                             // value of the bits of u above s, once s < bits
+    bool first = true;
+    while (s > 0) {
+        const int w = s > 8 ? 8 : s;
+        s -= w;
+        reinterpret_cast<uint4*>(wh)[2 * lane] = make_uint4(0, 0, 0, 0);
+        reinterpret_cast<uint4*>(wh)[2 * lane + 1] = make_uint4(0, 0, 0, 0);
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < NK; ++i) {
+            uint32_t m = key[i] != KEY_INELIGIBLE ? 1u : 0u;
+            if (!first) m &= ((u[i] >> (s + w)) == prefix) ? 1u : 0u;
+            asm volatile("{ .reg .pred q; setp.ne.u32 q, %1, 0; @q red.shared.add.u32 [%0], 1; }"
+                         :: "r"(waddr + (((u[i] >> s) & ((1u << w) - 1u)) << 2)), "r"(m) : "memory");
+        }
+        __syncwarp();
+        const uint4 b0 = reinterpret_cast<const uint4*>(wh)[2 * lane], b1 = reinterpret_cast<const uint4*>(wh)[2 * lane + 1];
+        const uint32_t b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+        uint32_t sum = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sum += b[j];
+        uint32_t incl = sum;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+        const uint32_t excl = incl - sum;
+        const bool mine = (uint32_t)k >= excl && (uint32_t)k < incl;
+        uint32_t bin = 0, r = 0;
+        if (mine) {
+            r = (uint32_t)k - excl; bool done = false;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (!done) { if (r < b[j]) { bin = 8 * lane + j; done = true; } else r -= b[j]; }
+        }
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, mine);
+        const int src = bal ? __ffs(bal) - 1 : 0;
+        bin = __shfl_sync(0xFFFFFFFFu, bin, src);
+        k = (int)__shfl_sync(0xFFFFFFFFu, r, src);
+        prefix = first ? bin : ((prefix << w) | bin);
+        first = false;
+        __syncwarp();
+    }
+    // every bit of u is decided: the values with u == target tie in p; k is now the rank among them
+    const uint32_t target = first ? 0u : prefix;
+    int nt = 0; uint32_t tk = KEY_INELIGIBLE;
+#pragma unroll
+    for (int i = 0; i < NK; ++i) if (u[i] == target) { ++nt; tk = key[i]; }
+    const int ties = __reduce_add_sync(0xFFFFFFFFu, nt);
+    if (ties == 1) return __reduce_min_sync(0xFFFFFFFFu, tk);         // the usual case
+    uint32_t pre = 0;                                                  // rare: exact counting search on the float keys of the ties
+    for (int bit = 31; bit >= 0; --bit) {
+        const uint32_t cand = pre | (1u << bit);
+        int c = 0;
+#pragma unroll
+        for (int i = 0; i < NK; ++i) c += (u[i] == target && key[i] < cand) ? 1 : 0;
+        c = __reduce_add_sync(0xFFFFFFFFu, c);
+        if (c <= k) pre = cand;
+    }
+    return pre;
 }
 
 // ---- CTA-wide exact selection: 3-pass radix select (11 + 11 + 10 bits) on a 2048-bin shared histogram.
@@ -353,7 +439,7 @@ __device__ __forceinline__ void block_median_keys(const uint32_t (&key)[NK], uin
 // smem flag byte of a tile pixel: bit0 mask, bit1 eligible (this frame), bit3 keep, bits 4-5 gain selector
 //   epix10ka selector: data bit 14;  jungfrau selector: 0,1,2 = g0,g1,g2, 3 = none
 template <int DET, int ROWS, int COLS, int NB, int NT>
-__global__ void __launch_bounds__(NT)
+__global__ void __launch_bounds__(NT, DET == 0 ? 2 : 1)      // epix10ka: two CTAs/SM (measured: 1.3x on the row medians)
 cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c)
 {
     constexpr int TR = ROWS / 2, TC = COLS / NB, CH = TC / 8, NCH = TR * CH, CPT = NCH / NT;
@@ -503,46 +589,37 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     }
 
     // ---- mode 2: per-column medians within the half (common_mode_cols: same guards)
-    // One warp takes CC columns at a time (lane = row mod 32), all CC radix selections interleaved.
+    // One warp per column (lane = row mod 32); radix select on a linear image of the values (warp_kth_linear).
     if (mode & 2) {
-        constexpr int NK = (TR + 31) / 32, CC = DET == 0 ? 4 : 1;      // measured: interleaving helps epix10ka, hurts jungfrau (register cap)
-        static_assert(TC % CC == 0, "columns per warp step");
+        constexpr int NK = (TR + 31) / 32;
         const int warp = tid >> 5;
-        for (int col0 = warp * CC; col0 < TC; col0 += NW * CC) {
-            uint32_t k[CC][NK]; int n[CC], k1[CC];
+        uint32_t* wh = whist + warp * 256;
+        for (int col = warp; col < TC; col += NW) {
+            uint32_t k[NK]; int cnt = 0;
 #pragma unroll
-            for (int q = 0; q < CC; ++q) {
-                int cnt = 0;
-#pragma unroll
-                for (int i = 0; i < NK; ++i) {
-                    const int r = lane + 32 * i;
-                    k[q][i] = KEY_INELIGIBLE;
-                    if (r < TR && (fl[r * ST + col0 + q] & 2u)) { k[q][i] = psr_f2key(a[r * ST + col0 + q]); ++cnt; }
-                }
-                n[q] = __reduce_add_sync(0xFFFFFFFFu, cnt);
-                k1[q] = n[q] > 0 ? (n[q] - 1) >> 1 : 0;
+            for (int i = 0; i < NK; ++i) {
+                const int r = lane + 32 * i;
+                k[i] = KEY_INELIGIBLE;
+                if (r < TR && (fl[r * ST + col] & 2u)) { k[i] = psr_f2key(a[r * ST + col]); ++cnt; }
             }
-            uint32_t lo[CC];
-            warp_kth_radix_multi<NK, CC>(k, k1, whist + warp * (CC * 256), lo);
+            const int n = __reduce_add_sync(0xFFFFFFFFu, cnt);
+            if (n > c.npix_min && n > 0) {                         // warp-uniform
+                const uint32_t lo = warp_kth_linear<NK>(k, (n - 1) >> 1, wh);
+                uint32_t hi = lo;
+                if ((n & 1) == 0) {                                // even count: the upper middle value
+                    int cle = 0; uint32_t mg = 0xFFFFFFFFu;
 #pragma unroll
-            for (int q = 0; q < CC; ++q) {
-                if (n[q] > c.npix_min && n[q] > 0) {
-                    uint32_t hi = lo[q];
-                    if ((n[q] & 1) == 0) {                              // even count: the upper middle value
-                        int cle = 0; uint32_t mg = 0xFFFFFFFFu;
+                    for (int i = 0; i < NK; ++i) { cle += (k[i] <= lo); if (k[i] > lo) mg = min(mg, k[i]); }
+                    cle = __reduce_add_sync(0xFFFFFFFFu, cle);
+                    mg = __reduce_min_sync(0xFFFFFFFFu, mg);
+                    if (cle <= (n >> 1)) hi = mg;
+                }
+                const float cm = psr_mid(psr_key2f(lo), psr_key2f(hi));
+                if (fabsf(cm) < c.cormax) {
 #pragma unroll
-                        for (int i = 0; i < NK; ++i) { cle += (k[q][i] <= lo[q]); if (k[q][i] > lo[q]) mg = min(mg, k[q][i]); }
-                        cle = __reduce_add_sync(0xFFFFFFFFu, cle);
-                        mg = __reduce_min_sync(0xFFFFFFFFu, mg);
-                        if (cle <= (n[q] >> 1)) hi = mg;
-                    }
-                    const float cm = psr_mid(psr_key2f(lo[q]), psr_key2f(hi));
-                    if (fabsf(cm) < c.cormax) {
-#pragma unroll
-                        for (int i = 0; i < NK; ++i) {
-                            const int r = lane + 32 * i;
-                            if (k[q][i] != KEY_INELIGIBLE) a[r * ST + col0 + q] = __fsub_rn(a[r * ST + col0 + q], cm);
-                        }
+                    for (int i = 0; i < NK; ++i) {
+                        const int r = lane + 32 * i;
+                        if (k[i] != KEY_INELIGIBLE) a[r * ST + col] = __fsub_rn(a[r * ST + col], cm);
                     }
                 }
             }
