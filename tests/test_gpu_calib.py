@@ -404,3 +404,23 @@ def test_common_mode_is_deterministic_over_repeated_launches(torch, kind, mode):
     for _ in range(12):
         assert torch.equal(cal.calib(d).view(torch.int32), first.view(torch.int32))
     kat.assert_same_bits(first[5].cpu().numpy(), oc.det_calib(spec.kind, raw[5], consts, (7, mode, 20.0, 10)))
+
+
+@pytest.mark.parametrize("kind,mode", [("epix", 2), ("epix", 7), ("jf", 3)])
+def test_common_mode_with_massive_ties(torch, kind, mode):
+    """Flat pedestals and few distinct ADC values: almost every value ties with many others, in floats and in the
+    linear image the column select works on -- the tie-breaking paths must still give NumPy's median exactly."""
+    spec = (syn.EPIX10K2M if kind == "epix" else syn.JUNGFRAU4M).with_nseg(1)
+    consts = syn.make_constants(spec, seed=400, bad_fraction=0.02, zero_gain_fraction=0.0)
+    consts["peds"][:] = 100.0
+    if "offs" in consts:
+        consts["offs"][:] = 0.25
+    rng = np.random.default_rng(401)
+    raw = rng.integers(98, 104, size=(2,) + spec.shape).astype(np.uint16)       # six distinct values
+    raw[1, :, :, ::7] = 100                                                     # long runs of one value
+    raw[1, 0, 5, :] = 16383                                                     # and a row of outliers stretching the range
+    cmpars = (7, mode, 50.0, 10)
+    cal = _calibrator(spec, consts)
+    cal.set_common_mode(cmpars)
+    got = cal.calib(_to_dev(torch, raw)).cpu().numpy()
+    kat.assert_same_bits(got, _oracle_batch(spec, raw, consts, cmpars), f"{kind} ties mode {mode}")
