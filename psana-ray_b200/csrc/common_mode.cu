@@ -922,7 +922,11 @@ cudaError_t psr_launch_common_mode(const PsrDev& c, const uint16_t* d_raw, int n
         else cm_calib_kernel<0, 352, 384, 8, EPIX_NT><<<grid, EPIX_NT, EPIX_SMEM, st>>>(d_raw, d_out, c);
     } else {
         const unsigned grid = (unsigned)nframes * c.nseg * 2 * 16;
-        if (c.cm_mode == 4) cm_banks_kernel<1, 512, 1024, 16, JF_NT, 1, 8><<<grid, JF_NT, 0, st>>>(d_raw, d_out, c);
+#ifndef PSR_CMB_JF_NT
+#define PSR_CMB_JF_NT 512
+#define PSR_CMB_JF_CW 8
+#endif
+        if (c.cm_mode == 4) cm_banks_kernel<1, 512, 1024, 16, PSR_CMB_JF_NT, 1, PSR_CMB_JF_CW><<<grid, PSR_CMB_JF_NT, 0, st>>>(d_raw, d_out, c);
         else cm_calib_kernel<1, 512, 1024, 16, JF_NT><<<grid, JF_NT, JF_SMEM, st>>>(d_raw, d_out, c);
     }
     return cudaGetLastError();
