@@ -118,6 +118,23 @@ class SyntheticSource:
         return pool[local_index % pool.shape[0]]
 
 
+def epix10ka_config_bytes(pixel_config, trbits, asic_quadrants=((1, 1), (0, 1), (0, 0), (1, 0))):
+    """Per-pixel config byte the library wants (``psr_set_constants`` ``h_cfg``) from what psana's epix10ka
+    configuration object holds for ONE segment: ``pixel_config`` = asicPixelConfigArray (rows, cols) whose bits 3,2
+    are the pixel gain configuration, ``trbits`` = the four ASICs' trbit values.  The trbit goes to bit 4 of every
+    pixel of its ASIC's quadrant, as psana's ``cbits_config_epix10ka`` does [EXT].  ``asic_quadrants[i]`` =
+    (row half, column half) of ASIC i; the default is the layout restated from psana (A0 bottom right, A1 top right,
+    A2 top left, A3 bottom left) and is a parameter because it could not be checked offline."""
+    pca = np.asarray(pixel_config)
+    rows, cols = pca.shape[-2:]
+    cfg = (pca & 0xC).astype(np.uint8)
+    rh, ch = rows // 2, cols // 2
+    for asic, (r, c) in enumerate(asic_quadrants):
+        if trbits[asic]:
+            cfg[..., r * rh:(r + 1) * rh, c * ch:(c + 1) * ch] |= 0x10
+    return cfg
+
+
 class PsanaSource:
     """psana-backed source (LCLS-I psana1).  Needs ``import psana``; raises ImportError otherwise."""
 

@@ -387,3 +387,19 @@ def test_iterable_dataset_yields_whole_batches(qroot):
         seen.append((int(rank), int(idx0), float(data.mean())))
     assert seen == [(0, 0, 0.0), (1, 5, 1.0), (0, 10, 2.0)]
     assert len(h.poll_released("o")) == 3
+
+
+def test_epix10ka_config_bytes_broadcasts_trbit_per_asic():
+    from psana_ray.event_source import epix10ka_config_bytes
+    from psana_ray.synthetic import EPIX10KA_MODE_LUT
+    pca = np.zeros((352, 384), dtype=np.uint16)
+    pca[:, :] = 0xFFF3                      # junk everywhere except bits 3,2 = 00 (auto-ranging)
+    pca[10, 20] = 0x000C                    # one fixed-high pixel
+    cfg = epix10ka_config_bytes(pca, trbits=[1, 0, 0, 1])
+    assert cfg.dtype == np.uint8 and cfg.shape == (352, 384)
+    assert cfg[300, 300] == 0x10 and cfg[300, 10] == 0x10          # A0 bottom right, A3 bottom left
+    assert cfg[10, 300] == 0x00 and cfg[10, 20] == 0x0C            # A1 top right (trbit 0), pixel config kept
+    # decode: trbit 1 + auto -> AHL-H (3) / AHL-L (5); trbit 0 + auto -> AML-M (4) / AML-L (6); fixed high, trbit 0 -> FM (1)
+    assert EPIX10KA_MODE_LUT[cfg[300, 300]] == 3 and EPIX10KA_MODE_LUT[cfg[300, 300] | 32] == 5
+    assert EPIX10KA_MODE_LUT[cfg[10, 300]] == 4 and EPIX10KA_MODE_LUT[cfg[10, 300] | 32] == 6
+    assert EPIX10KA_MODE_LUT[cfg[10, 20]] == 1
