@@ -267,10 +267,25 @@ constexpr int IMG_TW = 64, IMG_TH = 16;
 
 struct ImgGeom { int H, W; };
 
+// VEC (W % 4 == 0): every thread's 4 pixels are one aligned 16-byte store.  Otherwise the widest store the actual
+// address allows: image widths are arbitrary (1566 in the synthetic epix10k2M geometry: rows alternate between
+// 16- and 8-byte alignment), and scalar 4-byte stores halve the kernel.
 template <bool VEC>
-__device__ __forceinline__ void img_store(float* __restrict__ img, size_t off, int ncol, const float v[4]) {
-    if (VEC) { __stcs(reinterpret_cast<float4*>(img + off), make_float4(v[0], v[1], v[2], v[3])); }
-    else { for (int i = 0; i < ncol; ++i) __stcs(img + off + i, v[i]); }
+__device__ __forceinline__ void img_store(float* __restrict__ img, size_t off, int ncol, const float (&v)[4]) {
+    float* p = img + off;
+    if (VEC) { __stcs(reinterpret_cast<float4*>(p), make_float4(v[0], v[1], v[2], v[3])); return; }
+    const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+    if (ncol == 4 && (a & 15) == 0) {
+        __stcs(reinterpret_cast<float4*>(p), make_float4(v[0], v[1], v[2], v[3]));
+    } else if ((a & 7) == 0) {
+        if (ncol >= 2) __stcs(reinterpret_cast<float2*>(p), make_float2(v[0], v[1])); else if (ncol == 1) __stcs(p, v[0]);
+        if (ncol == 4) __stcs(reinterpret_cast<float2*>(p) + 1, make_float2(v[2], v[3])); else if (ncol == 3) __stcs(p + 2, v[2]);
+    } else {
+        if (ncol > 0) __stcs(p, v[0]);
+        if (ncol > 1) __stcs(p + 1, v[1]);
+        if (ncol > 2) __stcs(p + 2, v[2]);
+        if (ncol > 3) __stcs(p + 3, v[3]);
+    }
 }
 
 // +1: src[0..3] ascending, contiguous, src[0] % 4 == 0; -1: descending with src[3] % 4 == 0; 0: anything else.
@@ -326,7 +341,7 @@ __device__ __forceinline__ void img_tile_setup(ImgTile& t, const int32_t* __rest
 // v[u][0..3] = this thread's LOADED values of frames f0+u (u < nf) -> image, through shared memory when the
 // tile is transposed (all frames of the group share two barriers)
 #ifndef PSR_IMG_NU
-#define PSR_IMG_NU 1
+#define PSR_IMG_NU 2
 #endif
 constexpr int IMG_NU = PSR_IMG_NU;                              // frames per group: loads of the whole group are in flight together
 
@@ -520,7 +535,11 @@ cudaError_t psr_launch_decode(const PsrDev& c, const uint16_t* d_raw, int nframe
 cudaError_t psr_launch_image_gather(const PsrDev& c, const float* d_calib, int nframes, float* d_img, cudaStream_t st)
 {
     if (nframes <= 0) return cudaSuccess;
-    dim3 grid((c.W + IMG_TW - 1) / IMG_TW, (c.H + IMG_TH - 1) / IMG_TH, min(nframes, 8));
+    // the per-thread set-up (inverse-map lookups, run detection, tile vote) is amortised over the frames of one z slice
+#ifndef PSR_IMG_GZ
+#define PSR_IMG_GZ 8
+#endif
+    dim3 grid((c.W + IMG_TW - 1) / IMG_TW, (c.H + IMG_TH - 1) / IMG_TH, (nframes + PSR_IMG_GZ - 1) / PSR_IMG_GZ);
     if (c.W % 4 == 0)
         image_gather_kernel<true><<<grid, 256, 0, st>>>(d_calib, d_img, c.inv, c.keep_image, c.H, c.W, c.npix, nframes);
     else
