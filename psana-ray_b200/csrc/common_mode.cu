@@ -23,6 +23,18 @@
 #include "sortnet.cuh"
 
 // experiment switches (profiles/README.md records what each one measured)
+#ifndef PSR_CMB_JF_NT          /* jungfrau banks-only kernel: threads, pixels per chunk, min CTAs/SM */
+#define PSR_CMB_JF_NT 512
+#endif
+#ifndef PSR_CMB_JF_CW
+#define PSR_CMB_JF_CW 8
+#endif
+#ifndef PSR_CMB_JF_KS          /* keys parked in shared memory instead of registers: a second resident CTA per SM */
+#define PSR_CMB_JF_KS 1
+#endif
+#ifndef PSR_CMB_JF_MINB
+#define PSR_CMB_JF_MINB (PSR_CMB_JF_KS ? 2 : 1)
+#endif
 #ifndef PSR_CM_MATCH
 #define PSR_CM_MATCH 0
 #endif
@@ -245,12 +257,20 @@ __device__ __forceinline__ uint32_t warp_kth_linear(const uint32_t (&key)[NK], i
     return pre;
 }
 
+// Keys of one thread parked in shared memory instead of registers: slot i of thread t at base[i * NT + t]
+// (conflict-free), same [] syntax as a register array so the selection code serves both.
+template <int NT>
+struct SmemKeys {
+    uint32_t* base;                      // already offset by threadIdx.x
+    __device__ __forceinline__ uint32_t operator[](int i) const { return base[i * NT]; }
+};
+
 // ---- CTA-wide exact selection: 3-pass radix select (11 + 11 + 10 bits) on a 2048-bin shared histogram.
 // Keys stay in registers; bit i of `elig` says key[i] takes part.  Returns the k-th smallest (0-based)
 // eligible key; k must be < the number of eligible keys.  Every thread of the CTA must call it.
 // hist: 2048 words of shared memory; sh: 40 ints of shared memory (sh[34] = population of the chosen bin).
-template <int NT, int NKEY, int PASS>
-__device__ __forceinline__ void block_kth_pass(const uint32_t (&key)[NKEY], uint32_t elig, uint32_t& prefix, int& k,
+template <int NT, int NKEY, int PASS, typename K>
+__device__ __forceinline__ void block_kth_pass(const K& key, uint32_t elig, uint32_t& prefix, int& k,
                                                uint32_t* hist, int* sh)
 {
     constexpr int NB = 2048, BPT = (NB + NT - 1) / NT, NW = NT / 32;
@@ -305,8 +325,8 @@ __device__ __forceinline__ void block_kth_pass(const uint32_t (&key)[NKEY], uint
     k = sh[33];
 }
 
-template <int NT, int NKEY>
-__device__ __forceinline__ uint32_t block_kth(const uint32_t (&key)[NKEY], uint32_t elig, int k, uint32_t* hist, int* sh)
+template <int NT, int NKEY, typename K>
+__device__ __forceinline__ uint32_t block_kth(const K& key, uint32_t elig, int k, uint32_t* hist, int* sh)
 {
     for (int i = threadIdx.x; i < 2048; i += NT) hist[i] = 0u;
     __syncthreads();
@@ -326,8 +346,8 @@ __device__ __forceinline__ uint32_t block_kth(const uint32_t (&key)[NKEY], uint3
 // middle value outside the survivors) falls back to the register passes -- same exact answer.
 constexpr int LISTCAP = 1024;
 
-template <int NT, int NK, int NW>
-__device__ __forceinline__ void block_median_keys(const uint32_t (&key)[NK], uint32_t elig, int n, uint32_t* hist, int* sh,
+template <int NT, int NK, int NW, typename K>
+__device__ __forceinline__ void block_median_keys(const K& key, uint32_t elig, int n, uint32_t* hist, int* sh,
                                                   uint32_t* list, BlockRed<NW>& red, uint32_t& lo_out, uint32_t& hi_out)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -665,7 +685,7 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
 // thread keeps the keys of its CPT*8 pixels in registers from load to store; eligibility, gain
 // selector, mask and keep bits are packed in four 32-bit registers.
 // =================================================================================================
-template <int DET, int ROWS, int COLS, int NB, int NT, int MINB, int CW>
+template <int DET, int ROWS, int COLS, int NB, int NT, int MINB, int CW, bool KS>
 __global__ void __launch_bounds__(NT, MINB)
 cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c)
 {
@@ -686,7 +706,11 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     const uint16_t* rawf = raw + (size_t)frame * c.npix;
     float* outf = out + (size_t)frame * c.npix;
 
-    uint32_t key[NK];
+    // KS: the keys are parked in shared memory (slot q of thread t at skeys[q * NT + t]) instead of registers, which
+    // buys another resident CTA per SM
+    extern __shared__ uint32_t skeys[];
+    uint32_t keyr[KS ? 1 : NK];
+    SmemKeys<NT> keys{skeys + tid};
     uint32_t elig = 0, sel0 = 0, sel1 = 0;
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
@@ -723,7 +747,7 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
                 if (c.offs != nullptr) x = __fsub_rn(x, off);
                 el = (sel < 3 && ((c.elig_mask >> sel) & 1u) && (f & PSR_FL_MASK)) ? 1u : 0u;
             }
-            key[q] = psr_f2key(x);
+            if constexpr (KS) skeys[q * NT + tid] = psr_f2key(x); else keyr[q] = psr_f2key(x);
             elig |= (el ? 1u : 0u) << q;
             sel0 |= (sel & 1u) << q;
             if (DET != 0) sel1 |= (sel >> 1) << q;
@@ -736,11 +760,8 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     float cm = 0.f; bool apply = false;
     if (n >= c.npix_min && n > 0) {                        // uniform across the CTA
         uint32_t lo, hi;
-#ifdef PSR_CM_SKIPSEL      /* timing experiment only: wrong results */
-        lo = hi = key[0];
-#else
-        block_median_keys<NT, NK, NW>(key, elig, n, hist, selsh, list, red, lo, hi);
-#endif
+        if constexpr (KS) block_median_keys<NT, NK, NW>(keys, elig, n, hist, selsh, list, red, lo, hi);
+        else block_median_keys<NT, NK, NW>(keyr, elig, n, hist, selsh, list, red, lo, hi);
         cm = psr_mid(psr_key2f(lo), psr_key2f(hi));
         apply = !(fabsf(cm) > c.cormax);
     }
@@ -760,7 +781,8 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
         for (int i = 0; i < CW; ++i) {
             const int q = j * CW + i;
             const uint32_t f = (fw[i >> 2] >> (8 * (i & 3))) | (c.ignore_keep ? PSR_FL_KEEP : 0u);
-            float x = psr_key2f(key[q]);
+            float x;
+            if constexpr (KS) x = psr_key2f(keys[q]); else x = psr_key2f(keyr[q]);
             if (apply && ((elig >> q) & 1u)) x = __fsub_rn(x, cm);
             const uint32_t sel = ((sel0 >> q) & 1u) | (((sel1 >> q) & 1u) << 1);
             float gf;
@@ -885,7 +907,14 @@ cm_banks_epix_fi_kernel(const uint16_t* __restrict__ raw, float* __restrict__ ou
 constexpr int EPIX_NT = 352, JF_NT = 512;
 #ifndef PSR_CMB_EPIX_NT          /* banks-only kernel: threads, min CTAs/SM, pixels per chunk */
 #define PSR_CMB_EPIX_NT 352
-#define PSR_CMB_EPIX_MINB 2
+#endif
+#ifndef PSR_CMB_EPIX_KS        /* keys in shared memory: a third resident CTA per SM */
+#define PSR_CMB_EPIX_KS 1
+#endif
+#ifndef PSR_CMB_EPIX_MINB
+#define PSR_CMB_EPIX_MINB (PSR_CMB_EPIX_KS ? 3 : 2)
+#endif
+#ifndef PSR_CMB_EPIX_CW
 #define PSR_CMB_EPIX_CW 8
 #endif
 constexpr size_t EPIX_SMEM = ((size_t)(176 * 49) * 5 + 15) / 16 * 16 + (EPIX_NT / 32) * 4 * 256 * 4;   // padded tile (float + flag byte) + warp histograms
@@ -902,6 +931,10 @@ cudaError_t psr_common_mode_setup(void)
     cudaError_t e = cudaFuncSetAttribute(cm_calib_kernel<0, 352, 384, 8, EPIX_NT>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_SMEM);
     if (e != cudaSuccess) return e;
+    if (PSR_CMB_JF_KS) {
+        e = cudaFuncSetAttribute(cm_banks_kernel<1, 512, 1024, 16, PSR_CMB_JF_NT, PSR_CMB_JF_MINB, PSR_CMB_JF_CW, PSR_CMB_JF_KS != 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * 64 * 4);
+        if (e != cudaSuccess) return e;
+    }
     e = cudaFuncSetAttribute(cm_banks_epix_fi_kernel<EPIX_NT, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_FI_SMEM);
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(cm_calib_kernel<1, 512, 1024, 16, JF_NT>,
@@ -918,15 +951,11 @@ cudaError_t psr_launch_common_mode(const PsrDev& c, const uint16_t* d_raw, int n
             dim3 g2((unsigned)c.nseg * 2 * 8, (unsigned)((nframes + fpc - 1) / fpc));
             cm_banks_epix_fi_kernel<EPIX_NT, 2><<<g2, EPIX_NT, EPIX_FI_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
         }
-        else if (c.cm_mode == 4) cm_banks_kernel<0, 352, 384, 8, PSR_CMB_EPIX_NT, PSR_CMB_EPIX_MINB, PSR_CMB_EPIX_CW><<<grid, PSR_CMB_EPIX_NT, 0, st>>>(d_raw, d_out, c);
+        else if (c.cm_mode == 4) cm_banks_kernel<0, 352, 384, 8, PSR_CMB_EPIX_NT, PSR_CMB_EPIX_MINB, PSR_CMB_EPIX_CW, PSR_CMB_EPIX_KS != 0><<<grid, PSR_CMB_EPIX_NT, PSR_CMB_EPIX_KS ? 176 * 48 * 4 : 0, st>>>(d_raw, d_out, c);
         else cm_calib_kernel<0, 352, 384, 8, EPIX_NT><<<grid, EPIX_NT, EPIX_SMEM, st>>>(d_raw, d_out, c);
     } else {
         const unsigned grid = (unsigned)nframes * c.nseg * 2 * 16;
-#ifndef PSR_CMB_JF_NT
-#define PSR_CMB_JF_NT 512
-#define PSR_CMB_JF_CW 8
-#endif
-        if (c.cm_mode == 4) cm_banks_kernel<1, 512, 1024, 16, PSR_CMB_JF_NT, 1, PSR_CMB_JF_CW><<<grid, PSR_CMB_JF_NT, 0, st>>>(d_raw, d_out, c);
+        if (c.cm_mode == 4) cm_banks_kernel<1, 512, 1024, 16, PSR_CMB_JF_NT, PSR_CMB_JF_MINB, PSR_CMB_JF_CW, PSR_CMB_JF_KS != 0><<<grid, PSR_CMB_JF_NT, PSR_CMB_JF_KS ? 256 * 64 * 4 : 0, st>>>(d_raw, d_out, c);
         else cm_calib_kernel<1, 512, 1024, 16, JF_NT><<<grid, JF_NT, JF_SMEM, st>>>(d_raw, d_out, c);
     }
     return cudaGetLastError();
