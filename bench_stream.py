@@ -3,6 +3,7 @@
 with GPU-resident CUDA-IPC batch hand-off.
 
     python bench_stream.py --gpus N [--consumers M] [--events-per-rank E] [--batch 64] [--detector epix10k2M]
+    python bench_stream.py --impl reference [--events-per-rank E]     # configs[0]: the reference's CPU flow, 1 rank, queue_size 400
 
 Launches N producer ranks (the real CLI, `python -m psana_ray.producer --batch_source`, one per GPU) and M
 consumer processes (default one per GPU; consumer c maps the producers' slabs on GPU c %% N, so a consumer
@@ -43,8 +44,94 @@ print(json.dumps({"n": n, "t_first": t_first, "t_last": t_last, "sum": float(acc
 """
 
 
+# ---- reference arm: BASELINE.json configs[0], the reference's own per-event flow on the host cores -------------------------
+# One producer rank calibrates each event with the NumPy oracle (what `det.calib` does inside psana_wrapper's iter_events),
+# applies the two np.where masks (ref: producer.py:92-95), and puts the pickled [rank, idx, ndarray, photon_energy] item with the
+# reference's back-off (ref: producer.py:99-117); a consumer polls DataReader.read() (ref: examples/psana_consumer.py:28-47).
+# The queue server of this repo stands in for the detached Ray actor (Ray is not installable here).
+CPU_PRODUCER = r"""
+import sys, time
+sys.path.insert(0, %(pkg)r); sys.path.insert(0, %(root)r)
+import numpy as np
+from oracle import psana_calib as O                      # bench reference arm: the one place outside tests that runs the oracle
+from psana_ray import synthetic as S
+from psana_ray.shared_queue import create_queue, get_queue
+from psana_ray.producer import _backoff_put
+det, nev, qsize, ncons, pool = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), 16
+spec = S.detector_spec(det)
+consts = S.make_constants(spec, seed=0)
+consts["gfac"] = O.divide_protected(np.ones_like(consts["gain"]), consts["gain"])
+raw = S.make_raw_frames(spec, consts, pool, seed=1)
+bad = consts["mask"]; consts = dict(consts, mask=None)   # det.calib without mask; the producer applies it (--uses_bad_pixel_mask)
+create_queue("stream", "bench", maxsize=qsize)
+q = get_queue("stream", "bench")
+for idx in range(nev):
+    data = O.det_calib(spec.kind, raw[idx %% pool], consts)
+    data = O.producer_masks(data, bad_pixel_mask=bad)
+    if not _backoff_put(q, [0, idx, data, 9500.0], 1, None, 0, f"idx={idx}"):
+        sys.exit(2)
+for _ in range(ncons):
+    while not q.put(None):
+        time.sleep(0.01)
+"""
+
+CPU_CONSUMER = r"""
+import json, sys, time
+sys.path.insert(0, %(pkg)r)
+from psana_ray.data_reader import DataReader
+t_deadline = time.time() + 120
+while True:
+    try:
+        rd = DataReader(queue_name="stream", ray_namespace="bench"); rd.connect(); break
+    except ValueError:
+        if time.time() > t_deadline: raise
+        time.sleep(0.05)
+n = 0; acc = 0.0; t_first = None
+for rank, idx, data, photon_energy in rd:
+    if t_first is None: t_first = time.time()
+    acc += float(data.sum(dtype="float64")); n += 1
+t_last = time.time()
+rd.close()
+print(json.dumps({"n": n, "t_first": t_first, "t_last": t_last, "sum": acc}))
+"""
+
+
+def reference_arm(a):
+    root = tempfile.mkdtemp(prefix="psr_stream_ref_")
+    env = dict(os.environ, PSANA_RAY_DIR=root, CUDA_VISIBLE_DEVICES="")
+    ncons = a.consumers or 1
+    srcs = {}
+    for name, text in (("producer", CPU_PRODUCER), ("consumer", CPU_CONSUMER)):
+        srcs[name] = os.path.join(root, name + ".py")
+        with open(srcs[name], "w") as fh:
+            fh.write(text % {"pkg": PKG, "root": ROOT})
+    nev = a.events_per_rank
+    t_launch = time.time()
+    prod = subprocess.Popen([sys.executable, srcs["producer"], a.detector, str(nev), str(a.queue_size), str(ncons)], env=env)
+    cons = [subprocess.Popen([sys.executable, srcs["consumer"]], env=env, stdout=subprocess.PIPE, text=True) for _ in range(ncons)]
+    outs = [json.loads(c.communicate(timeout=900)[0].strip().splitlines()[-1]) for c in cons]
+    rc = prod.wait(timeout=60)
+    try:
+        sys.path.insert(0, PKG)
+        from psana_ray.shared_queue import get_queue
+        q = get_queue("stream", "bench", root); stats = q.stats(); q.shutdown()
+    except Exception:
+        stats = None
+    total = sum(o["n"] for o in outs)
+    t0 = min(o["t_first"] for o in outs if o["t_first"]); t1 = max(o["t_last"] for o in outs)
+    line = {"impl": "reference", "metric": "streamed calibrated frames/sec, producer -> queue -> consumer on the host", "value": total / (t1 - t0),
+            "unit": "frames/s", "n_gpus": 0, "producers": 1, "consumers": ncons, "events": total, "expected_events": nev, "seconds": t1 - t0,
+            "seconds_with_startup": t1 - t_launch, "producer_exit_codes": [rc], "queue_stats": stats,
+            "config": {"workload": "configs[0]: synthetic epix10k2M through producer -> shared_queue -> DataReader on CPU, 1 rank, NumPy calib",
+                       "detector": a.detector, "queue_size": a.queue_size, "queue": "this repo's unix-socket queue server standing in for the Ray actor",
+                       "cores": 1 + ncons}}
+    print(json.dumps(line), flush=True)
+    return 0 if total == nev and rc == 0 else 1
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"], help="reference = configs[0]: the reference's per-event CPU flow (1 rank, NumPy calib, pickled frames)")
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--consumers", type=int, default=0)
     ap.add_argument("--events-per-rank", type=int, default=2048)
@@ -54,6 +141,12 @@ def main():
     ap.add_argument("--image", action="store_true")
     ap.add_argument("--common-mode", default=None)
     a = ap.parse_args()
+    if a.impl == "reference":
+        if a.events_per_rank == 2048:
+            a.events_per_rank = 300                # ~15-30 s of NumPy calibration
+        if a.queue_size == 1024:
+            a.queue_size = 400                     # configs[0] / the reference README
+        return reference_arm(a)
     ncons = a.consumers or a.gpus
     root = tempfile.mkdtemp(prefix="psr_stream_")
     env = dict(os.environ, PSANA_RAY_DIR=root, PYTHONPATH=PKG + os.pathsep + os.environ.get("PYTHONPATH", ""), PSANA_RAY_DRAIN_S="120")

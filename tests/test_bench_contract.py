@@ -35,3 +35,13 @@ def test_gpu_arm_has_no_cpu_fallback():
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "3", "--no-cpu-baseline"],
                          capture_output=True, text=True, timeout=600)
     assert out.returncode != 0 and "no CPU fallback" in (out.stderr + out.stdout)
+
+
+def test_stream_reference_arm_streams_every_event_on_the_host():
+    """configs[0]: producer -> queue -> DataReader on CPU, one rank, NumPy calibration, pickled per-event items."""
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench_stream.py"), "--impl", "reference", "--events-per-rank", "6",
+                          "--queue-size", "4"], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr
+    d = json.loads(out.stdout.strip().splitlines()[-1])
+    assert d["impl"] == "reference" and d["events"] == d["expected_events"] == 6 and d["value"] > 0
+    assert d["queue_stats"]["get"] == 7 and d["config"]["queue_size"] == 4      # 6 events + 1 sentinel
