@@ -29,7 +29,7 @@ while True:
     except ValueError:
         if time.time() > t_deadline: raise
         time.sleep(0.05)
-n = 0; acc = torch.zeros((), dtype=torch.float64, device="cuda"); t_first = None
+n = 0; fb = 0; acc = torch.zeros((), dtype=torch.float64, device="cuda"); t_first = None
 while True:
     b = rd.read_batch()
     if b is None:
@@ -37,10 +37,10 @@ while True:
         time.sleep(0.0005); continue
     if t_first is None: t_first = time.time()
     acc += b[2].sum(dtype=torch.float64)          # the consumer really reads the frames
-    n += b[2].shape[0]
+    n += b[2].shape[0]; fb = b[2][0].numel() * 4
 torch.cuda.synchronize(); t_last = time.time()
 rd.close()
-print(json.dumps({"n": n, "t_first": t_first, "t_last": t_last, "sum": float(acc), "device": dev}))
+print(json.dumps({"n": n, "t_first": t_first, "t_last": t_last, "sum": float(acc), "device": dev, "frame_bytes": fb}))
 """
 
 
@@ -129,6 +129,56 @@ def reference_arm(a):
     return 0 if total == nev and rc == 0 else 1
 
 
+def bridge_arm(a):
+    """the cross-box leg, with two queue roots on one machine standing for two boxes."""
+    import socket
+    if a.gpus < 2:
+        print("--bridge needs --gpus 2 (NCCL refuses two ranks on one device)", file=sys.stderr)
+        return 2
+    ncons = a.consumers or 1
+    root_a, root_b = tempfile.mkdtemp(prefix="psr_boxA_"), tempfile.mkdtemp(prefix="psr_boxB_")
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]
+    base = dict(os.environ, PYTHONPATH=PKG + os.pathsep + os.environ.get("PYTHONPATH", ""), PSANA_RAY_DRAIN_S="120")
+    env_a, env_b = dict(base, PSANA_RAY_DIR=root_a), dict(base, PSANA_RAY_DIR=root_b)
+    cons_src = os.path.join(root_b, "consumer.py")
+    with open(cons_src, "w") as fh:
+        fh.write(CONSUMER % {"pkg": PKG})
+    nev = a.events_per_rank
+    pargs = ["--exp", "bench", "--run", "1", "--detector_name", a.detector, "--queue_name", "stream", "--ray_namespace", "bench",
+             "--queue_size", str(a.queue_size), "--batch_size", str(a.batch), "--num_events", str(nev), "--num_consumers", "1",
+             "--reliable_sentinels", "--batch_source", "--log_level", "WARNING"] + ([] if a.image else ["--calib"])
+    if a.common_mode:
+        pargs += ["--common_mode", a.common_mode]
+    bargs = ["--queue_name", "stream", "--ray_namespace", "bench", "--log_level", "WARNING"]
+    denv = dict(WORLD_SIZE="2", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    prod = subprocess.Popen([sys.executable, "-m", "psana_ray.producer"] + pargs, env=dict(env_a, RANK="0", WORLD_SIZE="1", LOCAL_RANK="0"))
+    tx = subprocess.Popen([sys.executable, "-m", "psana_ray.bridge", "--role", "send", "--device", "0"] + bargs, env=dict(env_a, RANK="0", **denv))
+    rx = subprocess.Popen([sys.executable, "-m", "psana_ray.bridge", "--role", "recv", "--device", "1", "--queue_size", str(a.queue_size),
+                           "--batch_size", str(a.batch), "--num_consumers", str(ncons)] + bargs, env=dict(env_b, RANK="1", **denv))
+    cons = [subprocess.Popen([sys.executable, cons_src, "1"], env=env_b, stdout=subprocess.PIPE, text=True) for _ in range(ncons)]
+    outs = [json.loads(c.communicate(timeout=240)[0].strip().splitlines()[-1]) for c in cons]
+    rcs = [p.wait(timeout=300) for p in (prod, tx, rx)]
+    sys.path.insert(0, PKG)
+    from psana_ray.shared_queue import get_queue
+    stats = {}
+    for name, root in (("A", root_a), ("B", root_b)):
+        try:
+            q = get_queue("stream", "bench", root); stats[name] = q.stats(); q.shutdown()
+        except Exception:
+            stats[name] = None
+    total = sum(o["n"] for o in outs)
+    t0 = min(o["t_first"] for o in outs if o["t_first"]); t1 = max(o["t_last"] for o in outs)
+    line = {"metric": "streamed calibrated frames/sec, producer -> queue A -> NCCL bridge -> queue B -> consumer", "value": total / (t1 - t0),
+            "unit": "frames/s", "n_gpus": 2, "producers": 1, "consumers": ncons, "events": total, "expected_events": nev, "seconds": t1 - t0,
+            "exit_codes": {"producer": rcs[0], "bridge_send": rcs[1], "bridge_recv": rcs[2]}, "queue_stats": stats,
+            "payload_GBps": total / (t1 - t0) * outs[0].get("frame_bytes", 0) / 1e9,
+            "config": {"workload": "SURVEY 8f n3: cross-box leg emulated on one machine (two queue roots), GPU 0 -> GPU 1 over NCCL send/recv",
+                       "detector": a.detector, "batch": a.batch, "queue_size": a.queue_size, "image": a.image, "common_mode": a.common_mode}}
+    print(json.dumps(line), flush=True)
+    return 0 if total == nev and all(r == 0 for r in rcs) else 1
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"], help="reference = configs[0]: the reference's per-event CPU flow (1 rank, NumPy calib, pickled frames)")
@@ -140,6 +190,8 @@ def main():
     ap.add_argument("--detector", default="epix10k2M")
     ap.add_argument("--image", action="store_true")
     ap.add_argument("--common-mode", default=None)
+    ap.add_argument("--bridge", action="store_true", help="two emulated boxes on one machine: producer + queue A on GPU 0, psana_ray.bridge "
+                    "(NCCL send/recv) to queue B, consumers on GPU 1; needs --gpus 2")
     a = ap.parse_args()
     if a.impl == "reference":
         if a.events_per_rank == 2048:
@@ -147,6 +199,8 @@ def main():
         if a.queue_size == 1024:
             a.queue_size = 400                     # configs[0] / the reference README
         return reference_arm(a)
+    if a.bridge:
+        return bridge_arm(a)
     ncons = a.consumers or a.gpus
     root = tempfile.mkdtemp(prefix="psr_stream_")
     env = dict(os.environ, PSANA_RAY_DIR=root, PYTHONPATH=PKG + os.pathsep + os.environ.get("PYTHONPATH", ""), PSANA_RAY_DRAIN_S="120")

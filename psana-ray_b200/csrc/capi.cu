@@ -309,6 +309,7 @@ int psr_set_geometry(psr_ctx* c, const int32_t* h_iX, const int32_t* h_iY) {
     const int H = mx + 1, W = my + 1;
     if ((size_t)H * W > ((size_t)1 << 31) - 1) return fail(PSR_E_INVALID, "image %dx%d too large", H, W);
     DeviceGuard g(c->device);
+    c->have_geometry = false;            // a failure below must not leave the old map's pointer live
     try {
         std::vector<int32_t> inv((size_t)H * W, -1);
         for (size_t i = 0; i < n; ++i) inv[(size_t)h_iX[i] * W + h_iY[i]] = (int32_t)i;   // flat C order: last writer wins
@@ -465,7 +466,10 @@ int psr_calib_batch_host(psr_ctx* c, const uint16_t* h_raw, int nframes, float* 
         PSR_CUDA(cudaStreamWaitEvent(p.s_comp, p.ev_in[s], 0));
         float* o = d_out ? d_out + (size_t)f0 * oelems : p.d_out[s];
         rc = launch_batch(c, p.d_raw[s], nf, o, out_kind, p.s_comp);
-        if (rc != PSR_OK) return rc;
+        if (rc != PSR_OK) {              // drain what is already queued on the caller's buffers before reporting
+            cudaStreamSynchronize(p.s_in); cudaStreamSynchronize(p.s_comp); cudaStreamSynchronize(p.s_out);
+            return rc;
+        }
         PSR_CUDA(cudaEventRecord(p.ev_comp[s], p.s_comp));
         if (h_out) {
             PSR_CUDA(cudaStreamWaitEvent(p.s_out, p.ev_comp[s], 0));

@@ -125,3 +125,57 @@ def test_ipc_event_handles():
     N.check(lib.psr_ipc_export_mem(p, mh))
     assert any(mh)
     N.check(lib.psr_device_free(p, 0))
+
+
+def test_bridge_over_nccl_between_two_gpus(tmp_path):
+    """producer + queue A on GPU 0 -> psana_ray.bridge (NCCL send/recv) -> queue B -> DataReader on GPU 1.
+    Two queue roots stand for two boxes; needs two devices (NCCL refuses two ranks on one)."""
+    import socket
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root_a, root_b = str(tmp_path / "boxA"), str(tmp_path / "boxB")
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]
+    nev, det = 12, "epix10k2M"
+    extra = ["--detector_name", det, "--queue_size", "16", "--batch_size", "4", "--num_events", str(nev), "--num_consumers", "1",
+             "--queue_name", "shared_queue", "--ray_namespace", "my", "--reliable_sentinels", "--calib", "--common_mode", "7,4,50,10"]
+    env_a, env_b = dict(os.environ, PSANA_RAY_DIR=root_a), dict(os.environ, PSANA_RAY_DIR=root_b)
+    benv = dict(WORLD_SIZE="2", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), PYTHONPATH=PKG + os.pathsep + os.environ.get("PYTHONPATH", ""),
+                PSANA_RAY_DRAIN_S="60")
+    bargs = [sys.executable, "-m", "psana_ray.bridge", "--queue_name", "shared_queue", "--ray_namespace", "my", "--log_level", "WARNING"]
+    procs = [_launch(env_a, 0, 1, extra),
+             subprocess.Popen(bargs + ["--role", "send", "--device", "0"], env=dict(env_a, RANK="0", **benv), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True),
+             subprocess.Popen(bargs + ["--role", "recv", "--device", "1", "--queue_size", "8", "--batch_size", "4", "--nslabs", "3"],
+                              env=dict(env_b, RANK="1", **benv), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)]
+    try:
+        t0 = time.time()
+        reader = DataReader(address=root_b, device=1)
+        while True:
+            try:
+                reader.connect(); break
+            except ValueError:
+                assert time.time() - t0 < 120 and all(p.poll() is None for p in procs), "a process died: " + "".join(p.stdout.read() for p in procs if p.poll() is not None)
+                time.sleep(0.2)
+        items = []
+        for rank, idx, data, energy in reader:                     # stops at the bridged sentinel
+            assert data.is_cuda and data.device.index == 1
+            items.append((rank, idx, data.cpu().numpy(), energy))
+        reader.close()
+        for p in procs:
+            assert p.wait(timeout=120) == 0, p.stdout.read()
+    finally:
+        for p in procs:
+            if p.poll() is None:
+                p.kill()
+        for root in (root_a, root_b):
+            try:
+                SQ.get_queue("shared_queue", "my", root).shutdown()
+            except Exception:
+                pass
+    assert [i[1] for i in items] == list(range(nev))
+    cmpars = (7, 4, 50.0, 10)
+    src = SyntheticSource("mfxl1038923", 58, det, rank=0, size=1, num_events=nev, common_mode=cmpars)
+    for rank, idx, data, energy in items:
+        assert rank == 0 and energy == src.photon_energy(idx)
+        kat.assert_same_bits(data, oc.det_calib(src.spec.kind, src.raw_event(idx), src.constants(), cmpars), f"bridged event {idx}")
