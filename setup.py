@@ -8,6 +8,6 @@ setuptools.setup(
     description="psana-ray hot path (detector calibration + producer->consumer streaming) for NVIDIA B200",
     package_dir={"": "psana-ray_b200"},
     packages=["psana_ray"],
-    entry_points={"console_scripts": ["psana-ray-producer=psana_ray.producer:main"]},
+    entry_points={"console_scripts": ["psana-ray-producer=psana_ray.producer:main", "psana-ray-bridge=psana_ray.bridge:main"]},
     python_requires=">=3.9",
 )

@@ -387,6 +387,39 @@ def test_full_size_batch64_properties(torch):
     assert float(med.abs().max()) < 0.6       # lower-median of a zero-median set is within one ADU step
 
 
+def test_batch_beyond_2_to_31_elements(torch):
+    """1 100 epix10k2M frames = 2.38 G output elements (9.5 GB): element offsets no longer fit 32 bits.  The batch repeats a
+    pool of 4 frames, so frame f must equal frame f % 4 bit for bit on every path (map, common mode, image)."""
+    spec = syn.EPIX10K2M
+    consts = syn.make_constants(spec, seed=95)
+    pool = syn.make_raw_frames(spec, consts, 4, seed=96)
+    n = 1100
+    assert n * spec.npix > 2 ** 31
+    d = _to_dev(torch, pool).repeat((n + 3) // 4, 1, 1, 1)[:n].contiguous()
+    cal = _calibrator(spec, consts)
+    hw = cal.set_geometry(*syn.make_pixel_index_arrays(spec))
+    for cm in (None, (7, 4, 50.0, 10)):
+        cal.set_common_mode(cm)
+        ref = cal.calib(d[:4])
+        for f in (0, 3):
+            kat.assert_same_bits(ref[f].cpu().numpy(), oc.det_calib(spec.kind, pool[f], consts, cm))
+        out = cal.calib(d)
+        assert out.shape == (n,) + spec.shape
+        for f0 in range(0, n, 4):
+            k = min(4, n - f0)
+            assert torch.equal(out[f0:f0 + k].view(torch.int32), ref[:k].view(torch.int32)), f"frames {f0}.. differ (cm={cm})"
+        del out
+    for cm in (None, (7, 4, 50.0, 10)):                   # fused raw -> image, and common mode -> scratch -> gather
+        cal.set_common_mode(cm)
+        ref = cal.calib(d[:4], image=True)
+        img = cal.calib(d, image=True)
+        assert img.shape[0] == n and tuple(img.shape[-2:]) == tuple(hw)
+        for f0 in range(0, n, 4):
+            k = min(4, n - f0)
+            assert torch.equal(img[f0:f0 + k].view(torch.int32), ref[:k].view(torch.int32)), f"image frames {f0}.. differ (cm={cm})"
+        del img
+
+
 # ---- race hunting without compute-sanitizer (closed on this pool): shared-memory hazards show up as run-to-run differences ----
 
 @pytest.mark.parametrize("kind,mode", [("epix", 4), ("epix", 7), ("jf", 4), ("jf", 7)])
