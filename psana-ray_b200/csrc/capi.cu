@@ -82,6 +82,8 @@ struct psr_ctx {
     void* d_consts = nullptr; size_t consts_bytes = 0;
     uint8_t* d_flags = nullptr;
     int32_t* d_inv = nullptr;
+    int32_t* d_fwd = nullptr; int32_t* d_gaps = nullptr;     // scatter side of the geometry (common mode fused with assembly)
+    std::vector<int32_t> h_fwd;                               // per source pixel: winning image index or INT32_MIN, before the image keep mask
     uint8_t* d_keep_image = nullptr;
     float* d_scratch = nullptr; size_t scratch_elems = 0;
     int frames_per_block = 0;      // 0 = auto: persistent balanced schedule; > 0 forces the (tile, frame chunk) grid
@@ -106,6 +108,22 @@ int rebuild_flags(psr_ctx* c) {
         fl[i] = (uint8_t)f;
     }
     PSR_CUDA(cudaMemcpy(c->d_flags, fl.data(), (size_t)n, cudaMemcpyHostToDevice));
+    return PSR_OK;
+}
+
+// device copy of the forward map with the image keep mask folded in (~index = "store 0 there")
+int upload_fwd(psr_ctx* c, const uint8_t* h_keep_image) {
+    const size_t n = c->h_fwd.size();
+    if (n == 0) return PSR_OK;
+    if (!c->d_fwd) PSR_CUDA(cudaMalloc(&c->d_fwd, n * sizeof(int32_t)));
+    if (!h_keep_image) {
+        PSR_CUDA(cudaMemcpy(c->d_fwd, c->h_fwd.data(), n * sizeof(int32_t), cudaMemcpyHostToDevice));
+    } else {
+        std::vector<int32_t> f(c->h_fwd);
+        for (size_t i = 0; i < n; ++i) if (f[i] >= 0 && !h_keep_image[f[i]]) f[i] = ~f[i];
+        PSR_CUDA(cudaMemcpy(c->d_fwd, f.data(), n * sizeof(int32_t), cudaMemcpyHostToDevice));
+    }
+    c->dev.fwd = c->d_fwd;
     return PSR_OK;
 }
 
@@ -140,6 +158,10 @@ int launch_batch(psr_ctx* c, const uint16_t* d_raw, int nframes, float* d_out, i
     } else {
         if (d.cm_mode == 0) {
             PSR_CUDA(psr_launch_image_fused(d, d_raw, nframes, d_out, fpb, st));
+        } else if (d.cm_mode == 4 && d.fwd != nullptr) {
+            // bank medians only: the common-mode kernel writes each tile straight into the images (no scratch, no second pass)
+            PsrDev t = d; t.ignore_keep = 1;
+            PSR_CUDA(psr_launch_common_mode_image(t, d_raw, nframes, d_out, st));
         } else {
             int rc = ensure_scratch(c, (size_t)nframes * d.npix);
             if (rc != PSR_OK) return rc;
@@ -217,6 +239,8 @@ void psr_destroy(psr_ctx* c) {
     if (c->d_consts) cudaFree(c->d_consts);
     if (c->d_flags) cudaFree(c->d_flags);
     if (c->d_inv) cudaFree(c->d_inv);
+    if (c->d_fwd) cudaFree(c->d_fwd);
+    if (c->d_gaps) cudaFree(c->d_gaps);
     if (c->d_keep_image) cudaFree(c->d_keep_image);
     if (c->d_scratch) cudaFree(c->d_scratch);
     delete c;
@@ -317,6 +341,24 @@ int psr_set_geometry(psr_ctx* c, const int32_t* h_iX, const int32_t* h_iY) {
         if (c->d_keep_image) { PSR_CUDA(cudaFree(c->d_keep_image)); c->d_keep_image = nullptr; c->dev.keep_image = nullptr; }
         PSR_CUDA(cudaMalloc(&c->d_inv, inv.size() * sizeof(int32_t)));
         PSR_CUDA(cudaMemcpy(c->d_inv, inv.data(), inv.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+        // scatter side: every source pixel that is the last writer of its target stores there, nobody else does
+        c->dev.fwd = nullptr; c->dev.gaps = nullptr; c->dev.ngaps = 0;
+        if (c->d_fwd) { PSR_CUDA(cudaFree(c->d_fwd)); c->d_fwd = nullptr; }
+        if (c->d_gaps) { PSR_CUDA(cudaFree(c->d_gaps)); c->d_gaps = nullptr; }
+        c->h_fwd.assign(n, INT32_MIN);
+        for (size_t i = 0; i < n; ++i) {
+            const size_t t = (size_t)h_iX[i] * W + h_iY[i];
+            if (inv[t] == (int32_t)i) c->h_fwd[i] = (int32_t)t;
+        }
+        std::vector<int32_t> gaps;
+        for (size_t t = 0; t < inv.size(); ++t) if (inv[t] < 0) gaps.push_back((int32_t)t);
+        if (!gaps.empty()) {
+            PSR_CUDA(cudaMalloc(&c->d_gaps, gaps.size() * sizeof(int32_t)));
+            PSR_CUDA(cudaMemcpy(c->d_gaps, gaps.data(), gaps.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+        }
+        int rc = upload_fwd(c, nullptr);
+        if (rc != PSR_OK) return rc;
+        c->dev.gaps = c->d_gaps; c->dev.ngaps = (int)gaps.size();
     } catch (const std::bad_alloc&) { return fail(PSR_E_NOMEM, "out of host memory"); }
     c->dev.inv = c->d_inv; c->dev.H = H; c->dev.W = W;
     c->have_geometry = true;
@@ -344,12 +386,13 @@ int psr_set_keep_mask(psr_ctx* c, const uint8_t* h_keep, size_t n, int out_kind)
     if (out_kind != PSR_OUT_IMAGE) return fail(PSR_E_INVALID, "out_kind = %d", out_kind);
     if (!c->have_geometry) return fail(PSR_E_INVALID, "image keep mask needs psr_set_geometry first");
     const size_t hw = (size_t)c->dev.H * c->dev.W;
-    if (!h_keep) { if (c->d_keep_image) { PSR_CUDA(cudaFree(c->d_keep_image)); c->d_keep_image = nullptr; } c->dev.keep_image = nullptr; return PSR_OK; }
+    if (!h_keep) { if (c->d_keep_image) { PSR_CUDA(cudaFree(c->d_keep_image)); c->d_keep_image = nullptr; } c->dev.keep_image = nullptr; return upload_fwd(c, nullptr); }
     if (n != hw) return fail(PSR_E_INVALID, "keep mask has %zu elements, image has %zu", n, hw);
     if (!c->d_keep_image) PSR_CUDA(cudaMalloc(&c->d_keep_image, hw));
     PSR_CUDA(cudaMemcpy(c->d_keep_image, h_keep, hw, cudaMemcpyHostToDevice));
     c->dev.keep_image = c->d_keep_image;
-    return PSR_OK;
+    try { return upload_fwd(c, h_keep); }
+    catch (const std::bad_alloc&) { return fail(PSR_E_NOMEM, "out of host memory"); }
 }
 
 int psr_reserve(psr_ctx* c, int max_frames) {

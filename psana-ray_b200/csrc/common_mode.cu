@@ -680,12 +680,93 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
 }
 
 
+// ---- image-mode epilogue: the tile's pixels go straight to their places in the assembled image -----------------
+// A run of CW consecutive floats at any 4-byte alignment (image rows need not be a multiple of 4 wide), with the
+// widest stores the address allows.
+template <int CW>
+__device__ __forceinline__ void img_store_run(float* p, const float (&o)[8])
+{
+    const unsigned a = (unsigned)(reinterpret_cast<uintptr_t>(p) >> 2) & 3u;
+    if (CW == 8) {
+        if (a == 0)      { __stcs(reinterpret_cast<float4*>(p), make_float4(o[0], o[1], o[2], o[3])); __stcs(reinterpret_cast<float4*>(p + 4), make_float4(o[4], o[5], o[6], o[7])); }
+        else if (a == 2) { __stcs(reinterpret_cast<float2*>(p), make_float2(o[0], o[1])); __stcs(reinterpret_cast<float4*>(p + 2), make_float4(o[2], o[3], o[4], o[5])); __stcs(reinterpret_cast<float2*>(p + 6), make_float2(o[6], o[7])); }
+        else if (a == 1) { __stcs(p, o[0]); __stcs(reinterpret_cast<float2*>(p + 1), make_float2(o[1], o[2])); __stcs(reinterpret_cast<float4*>(p + 3), make_float4(o[3], o[4], o[5], o[6])); __stcs(p + 7, o[7]); }
+        else             { __stcs(p, o[0]); __stcs(reinterpret_cast<float4*>(p + 1), make_float4(o[1], o[2], o[3], o[4])); __stcs(reinterpret_cast<float2*>(p + 5), make_float2(o[5], o[6])); __stcs(p + 7, o[7]); }
+    } else {
+        if (a == 0)      { __stcs(reinterpret_cast<float4*>(p), make_float4(o[0], o[1], o[2], o[3])); }
+        else if (a == 2) { __stcs(reinterpret_cast<float2*>(p), make_float2(o[0], o[1])); __stcs(reinterpret_cast<float2*>(p + 2), make_float2(o[2], o[3])); }
+        else if (a == 1) { __stcs(p, o[0]); __stcs(reinterpret_cast<float2*>(p + 1), make_float2(o[1], o[2])); __stcs(p + 3, o[3]); }
+        else             { __stcs(p, o[0]); __stcs(p + 1, o[1]); __stcs(reinterpret_cast<float2*>(p + 2), make_float2(o[2], o[3])); }
+    }
+}
+
+// one streaming store at base[t]: a single multiply-add forms the address (the compiler otherwise rebuilds the 64-bit
+// frame offset for every pixel)
+__device__ __forceinline__ void img_st_at(float* base, int32_t t, float v)
+{
+    asm volatile("{ .reg .u64 a; mad.wide.u32 a, %1, 4, %0; st.global.cs.f32 [a], %2; }" :: "l"(base), "r"(t), "f"(v) : "memory");
+}
+
+// Targets of one chunk (PsrDev::fwd): kind 1 = CW consecutive ascending image indices from t0, 2 = descending
+// down to t0 (panel rotated by 180 degrees), 3 = every pixel has a target of its own, anywhere (rotated by 90/270:
+// plain stores, nothing to test), 0 = some pixel lost a duplicate target or is masked in the image: tested one by one.
+template <int CW>
+__device__ __forceinline__ uint32_t img_chunk_kind(const int32_t* __restrict__ fwd_gp, int& t0)
+{
+    int32_t t[8];
+    const int4 a = __ldg(reinterpret_cast<const int4*>(fwd_gp));
+    t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w;
+    if (CW == 8) { const int4 b = __ldg(reinterpret_cast<const int4*>(fwd_gp) + 1); t[4] = b.x; t[5] = b.y; t[6] = b.z; t[7] = b.w; }
+    bool asc = true, desc = true, all = t[0] >= 0;
+#pragma unroll
+    for (int i = 1; i < CW; ++i) { asc = asc && t[i] == t[0] + i; desc = desc && t[i] == t[0] - i; all = all && t[i] >= 0; }
+    t0 = asc ? t[0] : t[CW - 1];
+    return !all ? 0u : asc ? 1u : desc ? 2u : 3u;
+}
+
+template <int CW>
+__device__ __forceinline__ void img_store_chunk(float* __restrict__ imgf, const int32_t* __restrict__ fwd_gp, uint32_t kind, int t0,
+                                                const float (&o)[8])
+{
+    if (kind == 1u) img_store_run<CW>(imgf + t0, o);
+    else if (kind == 2u) {
+        float r[8];
+#pragma unroll
+        for (int i = 0; i < CW; ++i) r[i] = o[CW - 1 - i];
+        img_store_run<CW>(imgf + t0, r);
+    } else {
+        int32_t t[8];
+        const int4 a = __ldg(reinterpret_cast<const int4*>(fwd_gp));
+        t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w;
+        if (CW == 8) { const int4 b = __ldg(reinterpret_cast<const int4*>(fwd_gp) + 1); t[4] = b.x; t[5] = b.y; t[6] = b.z; t[7] = b.w; }
+        if (kind == 3u) {
+#pragma unroll
+            for (int i = 0; i < CW; ++i) img_st_at(imgf, t[i], o[i]);
+        } else {
+#pragma unroll
+            for (int i = 0; i < CW; ++i) {
+                if (t[i] >= 0) img_st_at(imgf, t[i], o[i]);
+                else if (t[i] != INT32_MIN) img_st_at(imgf, ~t[i], 0.0f);     // the image keep mask drops this target
+            }
+        }
+    }
+}
+
+// image indices no detector pixel maps to: zero in every frame (ref: img_from_pixel_arrays starts from np.zeros)
+__global__ void __launch_bounds__(256) img_gap_fill_kernel(float* __restrict__ img, const int32_t* __restrict__ gaps, int ngaps, size_t fimg, int nframes)
+{
+    for (int f = blockIdx.y; f < nframes; f += gridDim.y) {
+        float* imgf = img + (size_t)f * fimg;
+        for (int g = blockIdx.x * blockDim.x + threadIdx.x; g < ngaps; g += gridDim.x * blockDim.x) __stcs(imgf + __ldg(gaps + g), 0.0f);
+    }
+}
+
 // =================================================================================================
 // mode 4 only (the per-bank 2-d median -- the usual setting): no shared-memory tile at all.  Each
 // thread keeps the keys of its CPT*8 pixels in registers from load to store; eligibility, gain
 // selector, mask and keep bits are packed in four 32-bit registers.
 // =================================================================================================
-template <int DET, int ROWS, int COLS, int NB, int NT, int MINB, int CW, bool KS>
+template <int DET, int ROWS, int COLS, int NB, int NT, int MINB, int CW, bool KS, bool IMG>
 __global__ void __launch_bounds__(NT, MINB)
 cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c)
 {
@@ -704,7 +785,7 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     const int seg = bid % c.nseg;
     const int frame = bid / c.nseg;
     const uint16_t* rawf = raw + (size_t)frame * c.npix;
-    float* outf = out + (size_t)frame * c.npix;
+    float* outf = out + (size_t)frame * (IMG ? (size_t)c.H * c.W : (size_t)c.npix);    // IMG: out is the batch of assembled images
 
     // KS: the keys are parked in shared memory (slot q of thread t at skeys[q * NT + t]) instead of registers, which
     // buys another resident CTA per SM
@@ -791,8 +872,13 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
             const float v = __fmul_rn(__fmul_rn(x, gf), (f & PSR_FL_MASK) ? 1.0f : 0.0f);
             o[i] = (f & PSR_FL_KEEP) ? v : 0.0f;
         }
-        __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
-        if (CW == 8) __stcs(reinterpret_cast<float4*>(outf + gp + 4), make_float4(o[4], o[5], o[6], o[7]));
+        if constexpr (IMG) {
+            int t0; const uint32_t kind = img_chunk_kind<CW>(c.fwd + gp, t0);
+            img_store_chunk<CW>(outf, c.fwd + gp, kind, t0, o);
+        } else {
+            __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
+            if (CW == 8) __stcs(reinterpret_cast<float4*>(outf + gp + 4), make_float4(o[4], o[5], o[6], o[7]));
+        }
     }
 }
 
@@ -803,7 +889,7 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
 // removes most of the per-frame constant traffic from L2 that bounded the one-frame-per-CTA kernel
 // (profiles/README.md: 394 of 702 us).  The gain factors of the epilogue still come from L2.
 // =================================================================================================
-template <int NT, int MINB>
+template <int NT, int MINB, bool IMG>
 __global__ void __launch_bounds__(NT, MINB)
 cm_banks_epix_fi_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c, int nframes, int fpc)
 {
@@ -840,11 +926,18 @@ cm_banks_epix_fi_kernel(const uint16_t* __restrict__ raw, float* __restrict__ ou
         f.x |= keep_or; f.y |= keep_or;
         sfl[ch] = f;
     }
+    // IMG: where each chunk goes in the assembled image is the same for every frame
+    int t0j[IMG ? CPT : 1]; uint32_t kinds = 0;
+    if constexpr (IMG) {
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) kinds |= img_chunk_kind<8>(c.fwd + gpj[j], t0j[j]) << (2 * j);
+    }
+    const size_t fout = IMG ? (size_t)c.H * c.W : (size_t)c.npix;
 
     BlockRed<NW> red{redbuf, 0};
     for (int frame = f_begin; frame < f_end; ++frame) {
         const uint16_t* rawf = raw + (size_t)frame * c.npix;
-        float* outf = out + (size_t)frame * c.npix;
+        float* outf = out + (size_t)frame * fout;
         uint32_t key[NK];
         uint32_t elig = 0, sel0 = 0;
 #pragma unroll
@@ -898,8 +991,11 @@ cm_banks_epix_fi_kernel(const uint16_t* __restrict__ raw, float* __restrict__ ou
                 const float v = __fmul_rn(__fmul_rn(x, gf), (f & PSR_FL_MASK) ? 1.0f : 0.0f);
                 o[i] = (f & PSR_FL_KEEP) ? v : 0.0f;
             }
-            __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
-            __stcs(reinterpret_cast<float4*>(outf + gp + 4), make_float4(o[4], o[5], o[6], o[7]));
+            if constexpr (IMG) img_store_chunk<8>(outf, c.fwd + gp, (kinds >> (2 * j)) & 3u, t0j[j], o);
+            else {
+                __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
+                __stcs(reinterpret_cast<float4*>(outf + gp + 4), make_float4(o[4], o[5], o[6], o[7]));
+            }
         }
     }
 }
@@ -932,31 +1028,63 @@ cudaError_t psr_common_mode_setup(void)
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_SMEM);
     if (e != cudaSuccess) return e;
     if (PSR_CMB_JF_KS) {
-        e = cudaFuncSetAttribute(cm_banks_kernel<1, 512, 1024, 16, PSR_CMB_JF_NT, PSR_CMB_JF_MINB, PSR_CMB_JF_CW, PSR_CMB_JF_KS != 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * 64 * 4);
+        e = cudaFuncSetAttribute(cm_banks_kernel<1, 512, 1024, 16, PSR_CMB_JF_NT, PSR_CMB_JF_MINB, PSR_CMB_JF_CW, PSR_CMB_JF_KS != 0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * 64 * 4);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(cm_banks_kernel<1, 512, 1024, 16, PSR_CMB_JF_NT, PSR_CMB_JF_MINB, PSR_CMB_JF_CW, PSR_CMB_JF_KS != 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * 64 * 4);
         if (e != cudaSuccess) return e;
     }
-    e = cudaFuncSetAttribute(cm_banks_epix_fi_kernel<EPIX_NT, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_FI_SMEM);
+    e = cudaFuncSetAttribute(cm_banks_epix_fi_kernel<EPIX_NT, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_FI_SMEM);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(cm_banks_epix_fi_kernel<EPIX_NT, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_FI_SMEM);
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(cm_calib_kernel<1, 512, 1024, 16, JF_NT>,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JF_SMEM);
 }
 
+namespace {
+template <bool IMG>
+cudaError_t launch_banks(const PsrDev& c, const uint16_t* d_raw, int nframes, float* d_out, cudaStream_t st)
+{
+    if (c.det_kind == 0) {
+        if (PSR_CM_FPC > 1 && nframes > 1) {
+            const int fpc = PSR_CM_FPC;
+            dim3 g2((unsigned)c.nseg * 2 * 8, (unsigned)((nframes + fpc - 1) / fpc));
+            cm_banks_epix_fi_kernel<EPIX_NT, 2, IMG><<<g2, EPIX_NT, EPIX_FI_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
+        } else {
+            const unsigned grid = (unsigned)nframes * c.nseg * 2 * 8;
+            cm_banks_kernel<0, 352, 384, 8, PSR_CMB_EPIX_NT, PSR_CMB_EPIX_MINB, PSR_CMB_EPIX_CW, PSR_CMB_EPIX_KS != 0, IMG>
+                <<<grid, PSR_CMB_EPIX_NT, PSR_CMB_EPIX_KS ? 176 * 48 * 4 : 0, st>>>(d_raw, d_out, c);
+        }
+    } else {
+        const unsigned grid = (unsigned)nframes * c.nseg * 2 * 16;
+        cm_banks_kernel<1, 512, 1024, 16, PSR_CMB_JF_NT, PSR_CMB_JF_MINB, PSR_CMB_JF_CW, PSR_CMB_JF_KS != 0, IMG>
+            <<<grid, PSR_CMB_JF_NT, PSR_CMB_JF_KS ? 256 * 64 * 4 : 0, st>>>(d_raw, d_out, c);
+    }
+    return cudaGetLastError();
+}
+}  // namespace
+
 cudaError_t psr_launch_common_mode(const PsrDev& c, const uint16_t* d_raw, int nframes, float* d_out, cudaStream_t st)
 {
     if (nframes <= 0) return cudaSuccess;
+    if (c.cm_mode == 4) return launch_banks<false>(c, d_raw, nframes, d_out, st);
     if (c.det_kind == 0) {
         const unsigned grid = (unsigned)nframes * c.nseg * 2 * 8;
-        if (c.cm_mode == 4 && PSR_CM_FPC > 1 && nframes > 1) {
-            const int fpc = PSR_CM_FPC;
-            dim3 g2((unsigned)c.nseg * 2 * 8, (unsigned)((nframes + fpc - 1) / fpc));
-            cm_banks_epix_fi_kernel<EPIX_NT, 2><<<g2, EPIX_NT, EPIX_FI_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
-        }
-        else if (c.cm_mode == 4) cm_banks_kernel<0, 352, 384, 8, PSR_CMB_EPIX_NT, PSR_CMB_EPIX_MINB, PSR_CMB_EPIX_CW, PSR_CMB_EPIX_KS != 0><<<grid, PSR_CMB_EPIX_NT, PSR_CMB_EPIX_KS ? 176 * 48 * 4 : 0, st>>>(d_raw, d_out, c);
-        else cm_calib_kernel<0, 352, 384, 8, EPIX_NT><<<grid, EPIX_NT, EPIX_SMEM, st>>>(d_raw, d_out, c);
+        cm_calib_kernel<0, 352, 384, 8, EPIX_NT><<<grid, EPIX_NT, EPIX_SMEM, st>>>(d_raw, d_out, c);
     } else {
         const unsigned grid = (unsigned)nframes * c.nseg * 2 * 16;
-        if (c.cm_mode == 4) cm_banks_kernel<1, 512, 1024, 16, PSR_CMB_JF_NT, PSR_CMB_JF_MINB, PSR_CMB_JF_CW, PSR_CMB_JF_KS != 0><<<grid, PSR_CMB_JF_NT, PSR_CMB_JF_KS ? 256 * 64 * 4 : 0, st>>>(d_raw, d_out, c);
-        else cm_calib_kernel<1, 512, 1024, 16, JF_NT><<<grid, JF_NT, JF_SMEM, st>>>(d_raw, d_out, c);
+        cm_calib_kernel<1, 512, 1024, 16, JF_NT><<<grid, JF_NT, JF_SMEM, st>>>(d_raw, d_out, c);
     }
     return cudaGetLastError();
+}
+
+cudaError_t psr_launch_common_mode_image(const PsrDev& c, const uint16_t* d_raw, int nframes, float* d_img, cudaStream_t st)
+{
+    if (nframes <= 0) return cudaSuccess;
+    if (c.cm_mode != 4 || c.fwd == nullptr) return cudaErrorInvalidValue;
+    if (c.ngaps > 0) {
+        dim3 g((unsigned)((c.ngaps + 256 * 8 - 1) / (256 * 8)), (unsigned)(nframes < 65535 ? nframes : 65535));
+        img_gap_fill_kernel<<<g, 256, 0, st>>>(d_img, c.gaps, c.ngaps, (size_t)c.H * c.W, nframes);
+    }
+    return launch_banks<true>(c, d_raw, nframes, d_img, st);
 }

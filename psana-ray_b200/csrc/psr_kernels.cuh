@@ -26,6 +26,10 @@ struct PsrDev {
     const int32_t* inv;            // H*W, source pixel or -1
     const uint8_t* keep_image;     // H*W or null
     int H, W;
+    // image mode, scatter side (common mode fused with the assembly): per SOURCE pixel its image index if it is the
+    // last writer of that target (>= 0), ~index if the image keep mask zeroes that target, INT32_MIN if another
+    // pixel wins the target; gaps = image indices no pixel maps to (they are zero-filled)
+    const int32_t* fwd; const int32_t* gaps; int ngaps;
     // common mode
     int cm_mode; float cormax; int npix_min; uint32_t elig_mask;
     int ignore_keep;               // 1: calib-layout keep mask not applied (image mode masks the 2-D image)
@@ -39,6 +43,8 @@ cudaError_t psr_launch_image_fused(const PsrDev& c, const uint16_t* d_raw, int n
                                    int frames_per_block, cudaStream_t st);
 cudaError_t psr_launch_image_gather(const PsrDev& c, const float* d_calib, int nframes, float* d_img, cudaStream_t st);
 cudaError_t psr_launch_common_mode(const PsrDev& c, const uint16_t* d_raw, int nframes, float* d_out, cudaStream_t st);
+// common mode + image assembly in one pass (bank medians only: cm_mode == 4; needs c.fwd / c.gaps)
+cudaError_t psr_launch_common_mode_image(const PsrDev& c, const uint16_t* d_raw, int nframes, float* d_img, cudaStream_t st);
 cudaError_t psr_common_mode_setup(void);   // raises the dynamic shared-memory limit once per device
 
 // ---- small device helpers -----------------------------------------------------------------------

@@ -305,6 +305,56 @@ def test_image_width_not_multiple_of_4(torch):
     kat.assert_same_bits(got[0], oc.det_image(spec.kind, raw[0], consts, iX, iY))
 
 
+@pytest.mark.parametrize("kind,nseg,nframes", [("epix", 16, 3), ("epix", 2, 1), ("jf", 8, 2), ("jf", 1, 1)])
+def test_bank_common_mode_fused_with_image_assembly(torch, kind, nseg, nframes):
+    """cm_mode 4 + image: the common-mode kernel stores each tile straight into the image (runs for panels at 0/180
+    degrees, scalar stores for 90/270, nothing from pixels that lose a duplicate target) and a gap-fill pass zeroes the rest.
+    The output buffer starts as NaN so every pixel of every frame must have been written."""
+    spec = (syn.EPIX10K2M if kind == "epix" else syn.JUNGFRAU4M).with_nseg(nseg)
+    consts = syn.make_constants(spec, seed=65, cfg_variant="mixed")
+    raw = syn.make_raw_frames(spec, consts, nframes, seed=66)
+    iX, iY = syn.make_pixel_index_arrays(spec)
+    cm = (7, 4, 50.0, 10)
+    cal = _calibrator(spec, consts)
+    cal.set_common_mode(cm)
+    H, W = cal.set_geometry(iX, iY)
+    exp = np.stack([oc.det_image(spec.kind, raw[f], consts, iX, iY, cm) for f in range(nframes)])
+    out = torch.full(cal.out_shape(nframes, True), float("nan"), device="cuda")
+    cal.calib(_to_dev(torch, raw), out=out, image=True)
+    kat.assert_same_bits(out.cpu().numpy().reshape(exp.shape), exp, "fused image")
+    keep = np.random.default_rng(67).random((H, W)) > 0.2
+    cal.set_keep_mask(keep, image=True)
+    out.fill_(float("nan"))
+    cal.calib(_to_dev(torch, raw), out=out, image=True)
+    exp_k = np.stack([oc.producer_masks(exp[f], None, keep)[0] for f in range(nframes)])
+    kat.assert_same_bits(out.cpu().numpy().reshape(exp_k.shape), exp_k, "fused image + keep")
+    cal.set_keep_mask(None, image=True)
+    out.fill_(float("nan"))
+    cal.calib(_to_dev(torch, raw), out=out, image=True)
+    kat.assert_same_bits(out.cpu().numpy().reshape(exp.shape), exp, "fused image, keep cleared")
+
+
+@pytest.mark.parametrize("shift", [0, 1, 2, 3])
+def test_fused_image_runs_at_every_store_alignment(torch, shift):
+    """Identity geometry shifted by 0..3 columns in an image 389 wide: ascending runs start at every 4-byte alignment."""
+    spec = syn.EPIX10K2M.with_nseg(1)
+    consts = syn.make_constants(spec, seed=68)
+    raw = syn.make_raw_frames(spec, consts, 2, seed=69)
+    r, c = np.meshgrid(np.arange(spec.rows), np.arange(spec.cols), indexing="ij")
+    iX = (r[None] + 1).astype(np.int32); iY = (c[None] + shift).astype(np.int32)
+    iY[0, -1, -1] = 388                                                   # fixes W = 389 (odd) for every shift
+    cm = (7, 4, 50.0, 10)
+    for flip in (False, True):                                            # flipped: descending runs (panel rotated by 180)
+        jY = (388 - iY).astype(np.int32) if flip else iY
+        cal = _calibrator(spec, consts)
+        cal.set_common_mode(cm)
+        assert cal.set_geometry(iX, jY) == (353, int(jY.max()) + 1)
+        out = torch.full(cal.out_shape(2, True), float("nan"), device="cuda")
+        cal.calib(_to_dev(torch, raw), out=out, image=True)
+        exp = np.stack([oc.det_image(spec.kind, raw[f], consts, iX, jY, cm) for f in range(2)])
+        kat.assert_same_bits(out.cpu().numpy().reshape(exp.shape), exp, f"shift {shift} flip {flip}")
+
+
 # ---- host-fed pipeline, edge cases, errors ---------------------------------------------------------------
 
 def test_host_pipeline_equals_device_path(torch):
