@@ -95,13 +95,16 @@ int psr_image_shape(const psr_ctx* ctx, int* H, int* W);
  * output frame of `out_kind`.  NULL clears. */
 int psr_set_keep_mask(psr_ctx* ctx, const uint8_t* h_keep, size_t n, int out_kind);
 
-/* Pre-size the context's scratch (image mode with common mode on needs a calibrated-frame
- * scratch of max_frames) so that psr_calib_batch never allocates. */
+/* Pre-size the context's scratch (image mode with a common-mode word other than 4 goes through a
+ * calibrated-frame scratch of max_frames; bank medians alone -- word 4 -- and no common mode write the
+ * image directly) so that psr_calib_batch never allocates. */
 int psr_reserve(psr_ctx* ctx, int max_frames);
 
 /* Tuning knobs that change speed, never results.  "frames_per_block": frames one CTA of the
  * streaming kernels walks with its constants held in registers: 0 = auto (whole batch, at most 64),
- * > 0 = that many, < 0 = persistent schedule (one equal share of the batch per resident CTA). */
+ * > 0 = that many, < 0 = persistent schedule (one equal share of the batch per resident CTA).
+ * "image_gather": 1 = PSR_OUT_IMAGE without common mode runs the output-driven gather kernel instead of
+ * the source-driven scatter kernel (0, default). */
 int psr_set_option(psr_ctx* ctx, const char* name, int value);
 
 /* THE HOT CALL.  Replaces, for a whole batch at once, det.calib(evt) / det.image(evt) inside

@@ -462,6 +462,144 @@ image_fused_kernel(const uint16_t* __restrict__ raw, float* __restrict__ img, Ps
     }
 }
 
+
+// =================================================================================================
+// K4s: raw -> assembled image, SOURCE-driven (no common mode).  The map kernels' structure -- a thread
+// owns 4 pixels, holds their constants in registers and walks the frames of the batch -- with the image
+// index of every owned pixel (PsrDev::fwd, the scatter side of the geometry) held in registers too, so
+// the calibrated values go straight to their places: 12 + ~3 thread-instructions per pixel against 36 for
+// the output-driven gather.  Four CTAs share a tile of 32 rows x 128 pixels; which quarter a CTA takes and which
+// pixels of it a warp owns depends on how the tile lies in the image (see `rot` below), so that stores cover whole image-row pieces either way.
+// Neighbouring CTAs run concurrently on neighbouring tiles and the same frames, so sectors shared across a
+// tile border are completed in L2.  Gaps are zeroed by psr_launch_image_gap_fill.
+// =================================================================================================
+#ifndef PSR_IMGS_UNROLL
+#define PSR_IMGS_UNROLL 4
+#endif
+#ifndef PSR_IMGS_MINB
+#define PSR_IMGS_MINB 3
+#endif
+
+__device__ __forceinline__ void imgs_st_at(float* base, int32_t t, float v)
+{
+    asm volatile("{ .reg .u64 a; mad.wide.u32 a, %1, 4, %0; st.global.cs.f32 [a], %2; }" :: "l"(base), "r"(t), "f"(v) : "memory");
+}
+
+// 4 consecutive floats at any 4-byte alignment
+__device__ __forceinline__ void imgs_store_run4(float* p, float o0, float o1, float o2, float o3)
+{
+    const unsigned a = (unsigned)(reinterpret_cast<uintptr_t>(p) >> 2) & 3u;
+    if (a == 0)      { __stcs(reinterpret_cast<float4*>(p), make_float4(o0, o1, o2, o3)); }
+    else if (a == 2) { __stcs(reinterpret_cast<float2*>(p), make_float2(o0, o1)); __stcs(reinterpret_cast<float2*>(p + 2), make_float2(o2, o3)); }
+    else if (a == 1) { __stcs(p, o0); __stcs(reinterpret_cast<float2*>(p + 1), make_float2(o1, o2)); __stcs(p + 3, o3); }
+    else             { __stcs(p, o0); __stcs(p + 1, o1); __stcs(reinterpret_cast<float2*>(p + 2), make_float2(o2, o3)); }
+}
+
+template <int DET, bool HAS_OFFS>
+__global__ void __launch_bounds__(256, PSR_IMGS_MINB)
+image_scatter_kernel(const uint2* __restrict__ raw, float* __restrict__ img, PsrDev c, int nframes, int fpb)
+{
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int tiles_x = c.cols / 128, tiles_y = c.rows / 32;
+    int b = blockIdx.x;
+    const int tx = b % tiles_x; b /= tiles_x;
+    const int ty = b % tiles_y; const int seg = b / tiles_y;
+    const int pass = blockIdx.y & 3;                   // quarter of the 32 x 128 tile this CTA takes
+    const int ngroups = c.npix / 4;
+    // Which way the tile lies in the image decides who owns what (a speed matter only: any ownership is correct).
+    // Unrotated / 180 degrees: the CTA takes 8 rows of the tile, a warp one row of 128 pixels -- exactly the calib map
+    // kernel's pattern: 256 contiguous bytes of raw and 512 contiguous bytes of image per warp instruction.
+    // Rotated by 90 / 270 degrees (detector rows run along image columns): the CTA takes 32 columns of the tile, a warp
+    // 4 pixels of 32 consecutive ROWS, so each of its four scalar stores is 32 consecutive floats of one image row; the
+    // 8-byte raw loads of a warp then touch 32 sectors a quarter each, and the other three quarters are what the CTA's
+    // neighbouring warps load -- those loads go through L1 instead of streaming past it.
+    bool rot;
+    {
+        const int4 pt = __ldg(reinterpret_cast<const int4*>(c.fwd) + (((seg * c.rows + ty * 32) * c.cols + tx * 128) >> 2));
+        const int d = pt.y - pt.x;
+        rot = pt.x >= 0 && pt.y >= 0 && d != 1 && d != -1;
+    }
+    const int row = ty * 32 + (rot ? lane : pass * 8 + w);
+    const int col = tx * 128 + (rot ? pass * 32 + w * 4 : lane * 4);
+    const int g = ((seg * c.rows + row) * c.cols + col) >> 2;
+    const size_t fimg = (size_t)c.H * c.W;
+
+    // per-run constants of the 4 owned pixels, in registers for the whole batch
+    float P[4][DET == 0 ? 2 : 3], G[4][DET == 0 ? 2 : 3], O[4][3];
+    if (DET == 0) {
+        const float4 p0 = __ldg(reinterpret_cast<const float4*>(c.ped0) + g), q0 = __ldg(reinterpret_cast<const float4*>(c.gf0) + g);
+        const float4 p1 = __ldg(reinterpret_cast<const float4*>(c.ped1) + g), q1 = __ldg(reinterpret_cast<const float4*>(c.gf1) + g);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { P[i][0] = f4get(p0, i); P[i][1] = f4get(p1, i); G[i][0] = f4get(q0, i); G[i][1] = f4get(q1, i); }
+    } else {
+#pragma unroll
+        for (int m = 0; m < 3; ++m) {
+            const float4 p = __ldg(reinterpret_cast<const float4*>(c.peds) + (size_t)m * ngroups + g);
+            const float4 q = __ldg(reinterpret_cast<const float4*>(c.gfac) + (size_t)m * ngroups + g);
+            float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (HAS_OFFS) o = __ldg(reinterpret_cast<const float4*>(c.offs) + (size_t)m * ngroups + g);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { P[i][m] = f4get(p, i); G[i][m] = f4get(q, i); O[i][m] = f4get(o, i); }
+        }
+    }
+    // image mode: the calib-layout keep mask does not apply (ref: producer.py:92-97 masks the 2-D image)
+    const uint32_t fl = __ldg(reinterpret_cast<const uint32_t*>(c.flags) + g) | 0x08080808u;
+    const int4 t4 = __ldg(reinterpret_cast<const int4*>(c.fwd) + g);
+    const int32_t t[4] = {t4.x, t4.y, t4.z, t4.w};
+    const bool all = t[0] >= 0 && t[1] >= 0 && t[2] >= 0 && t[3] >= 0;
+    const bool asc = all && t[1] == t[0] + 1 && t[2] == t[0] + 2 && t[3] == t[0] + 3;
+    const bool desc = all && t[1] == t[0] - 1 && t[2] == t[0] - 2 && t[3] == t[0] - 3;
+    const int kind = asc ? 1 : desc ? 2 : all ? 3 : 0;
+
+    const int f_begin = (blockIdx.y >> 2) * fpb, f_end = min(nframes, f_begin + fpb);
+    auto frames = [&](int f, auto nconst) {
+        constexpr int NF = decltype(nconst)::value;
+        uint2 r[NF];
+#pragma unroll
+        for (int u = 0; u < NF; ++u) r[u] = rot ? __ldg(raw + (size_t)(f + u) * ngroups + g) : ld_raw(raw + (size_t)(f + u) * ngroups + g);
+#pragma unroll
+        for (int u = 0; u < NF; ++u) {
+            float o[4];
+            if (DET == 0) {
+                o[0] = epix_px(r[u].x & 0xFFFFu, P[0][0], G[0][0], P[0][1], G[0][1], fl);
+                o[1] = epix_px(r[u].x >> 16,     P[1][0], G[1][0], P[1][1], G[1][1], fl >> 8);
+                o[2] = epix_px(r[u].y & 0xFFFFu, P[2][0], G[2][0], P[2][1], G[2][1], fl >> 16);
+                o[3] = epix_px(r[u].y >> 16,     P[3][0], G[3][0], P[3][1], G[3][1], fl >> 24);
+            } else {
+                o[0] = jf_px<HAS_OFFS>(r[u].x & 0xFFFFu, P[0], O[0], G[0], fl);
+                o[1] = jf_px<HAS_OFFS>(r[u].x >> 16,     P[1], O[1], G[1], fl >> 8);
+                o[2] = jf_px<HAS_OFFS>(r[u].y & 0xFFFFu, P[2], O[2], G[2], fl >> 16);
+                o[3] = jf_px<HAS_OFFS>(r[u].y >> 16,     P[3], O[3], G[3], fl >> 24);
+            }
+            float* imgf = img + (size_t)(f + u) * fimg;
+            if (kind == 1) imgs_store_run4(imgf + t[0], o[0], o[1], o[2], o[3]);
+            else if (kind == 2) imgs_store_run4(imgf + t[3], o[3], o[2], o[1], o[0]);
+            else if (kind == 3) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) imgs_st_at(imgf, t[i], o[i]);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    if (t[i] >= 0) imgs_st_at(imgf, t[i], o[i]);
+                    else if (t[i] != INT32_MIN) imgs_st_at(imgf, ~t[i], 0.0f);      // the image keep mask drops this target
+                }
+            }
+        }
+    };
+    int f = f_begin;
+    for (; f + PSR_IMGS_UNROLL <= f_end; f += PSR_IMGS_UNROLL) frames(f, IntC<PSR_IMGS_UNROLL>{});
+    for (; f < f_end; ++f) frames(f, IntC<1>{});
+}
+
+// image indices no detector pixel maps to: zero in every frame (ref: img_from_pixel_arrays starts from np.zeros)
+__global__ void __launch_bounds__(256) img_gap_fill_kernel(float* __restrict__ img, const int32_t* __restrict__ gaps, int ngaps, size_t fimg, int nframes)
+{
+    for (int f = blockIdx.y; f < nframes; f += gridDim.y) {
+        float* imgf = img + (size_t)f * fimg;
+        for (int g = blockIdx.x * blockDim.x + threadIdx.x; g < ngaps; g += gridDim.x * blockDim.x) __stcs(imgf + __ldg(gaps + g), 0.0f);
+    }
+}
+
 }  // namespace
 
 // ---- launchers --------------------------------------------------------------------------------
@@ -561,3 +699,28 @@ cudaError_t psr_launch_image_fused(const PsrDev& c, const uint16_t* d_raw, int n
 #undef PSR_IMG_LAUNCH
     return cudaGetLastError();
 }
+
+cudaError_t psr_launch_image_gap_fill(const PsrDev& c, int nframes, float* d_img, cudaStream_t st)
+{
+    if (nframes <= 0 || c.ngaps <= 0) return cudaSuccess;
+    dim3 g((unsigned)((c.ngaps + 256 * 8 - 1) / (256 * 8)), (unsigned)(nframes < 65535 ? nframes : 65535));
+    img_gap_fill_kernel<<<g, 256, 0, st>>>(d_img, c.gaps, c.ngaps, (size_t)c.H * c.W, nframes);
+    return cudaGetLastError();
+}
+
+cudaError_t psr_launch_image_scatter(const PsrDev& c, const uint16_t* d_raw, int nframes, float* d_img,
+                                     int fpb, cudaStream_t st)
+{
+    if (nframes <= 0) return cudaSuccess;
+    if (c.fwd == nullptr || c.rows % 32 != 0 || c.cols % 128 != 0) return cudaErrorInvalidValue;
+    cudaError_t e = psr_launch_image_gap_fill(c, nframes, d_img, st);
+    if (e != cudaSuccess) return e;
+    if (fpb <= 0 || fpb > nframes) fpb = nframes > 64 ? 64 : nframes;
+    dim3 grid((unsigned)(c.nseg * (c.rows / 32) * (c.cols / 128)), 4u * (unsigned)((nframes + fpb - 1) / fpb));
+    const uint2* r = reinterpret_cast<const uint2*>(d_raw);
+    if (c.det_kind == 0) image_scatter_kernel<0, false><<<grid, 256, 0, st>>>(r, d_img, c, nframes, fpb);
+    else if (c.offs != nullptr) image_scatter_kernel<1, true><<<grid, 256, 0, st>>>(r, d_img, c, nframes, fpb);
+    else image_scatter_kernel<1, false><<<grid, 256, 0, st>>>(r, d_img, c, nframes, fpb);
+    return cudaGetLastError();
+}
+

@@ -86,6 +86,7 @@ struct psr_ctx {
     std::vector<int32_t> h_fwd;                               // per source pixel: winning image index or INT32_MIN, before the image keep mask
     uint8_t* d_keep_image = nullptr;
     float* d_scratch = nullptr; size_t scratch_elems = 0;
+    int image_gather = 0;          // 1: raw -> image through the output-driven gather kernel instead of the scatter kernel
     int frames_per_block = 0;      // 0 = auto: persistent balanced schedule; > 0 forces the (tile, frame chunk) grid
     HostPipe pipe;
 };
@@ -157,7 +158,8 @@ int launch_batch(psr_ctx* c, const uint16_t* d_raw, int nframes, float* d_out, i
         else                PSR_CUDA(psr_launch_common_mode(d, d_raw, nframes, d_out, st));
     } else {
         if (d.cm_mode == 0) {
-            PSR_CUDA(psr_launch_image_fused(d, d_raw, nframes, d_out, fpb, st));
+            if (d.fwd != nullptr && !c->image_gather) PSR_CUDA(psr_launch_image_scatter(d, d_raw, nframes, d_out, fpb, st));
+            else PSR_CUDA(psr_launch_image_fused(d, d_raw, nframes, d_out, fpb, st));
         } else if (d.cm_mode == 4 && d.fwd != nullptr) {
             // bank medians only: the common-mode kernel writes each tile straight into the images (no scratch, no second pass)
             PsrDev t = d; t.ignore_keep = 1;
@@ -404,6 +406,7 @@ int psr_reserve(psr_ctx* c, int max_frames) {
 int psr_set_option(psr_ctx* c, const char* name, int value) {
     if (!c || !name) return fail(PSR_E_INVALID, "null argument");
     if (!strcmp(name, "frames_per_block")) { c->frames_per_block = value; return PSR_OK; }
+    if (!strcmp(name, "image_gather")) { c->image_gather = value != 0; return PSR_OK; }
     return fail(PSR_E_INVALID, "unknown option %s", name);
 }
 

@@ -752,15 +752,6 @@ __device__ __forceinline__ void img_store_chunk(float* __restrict__ imgf, const 
     }
 }
 
-// image indices no detector pixel maps to: zero in every frame (ref: img_from_pixel_arrays starts from np.zeros)
-__global__ void __launch_bounds__(256) img_gap_fill_kernel(float* __restrict__ img, const int32_t* __restrict__ gaps, int ngaps, size_t fimg, int nframes)
-{
-    for (int f = blockIdx.y; f < nframes; f += gridDim.y) {
-        float* imgf = img + (size_t)f * fimg;
-        for (int g = blockIdx.x * blockDim.x + threadIdx.x; g < ngaps; g += gridDim.x * blockDim.x) __stcs(imgf + __ldg(gaps + g), 0.0f);
-    }
-}
-
 // =================================================================================================
 // mode 4 only (the per-bank 2-d median -- the usual setting): no shared-memory tile at all.  Each
 // thread keeps the keys of its CPT*8 pixels in registers from load to store; eligibility, gain
@@ -1082,9 +1073,7 @@ cudaError_t psr_launch_common_mode_image(const PsrDev& c, const uint16_t* d_raw,
 {
     if (nframes <= 0) return cudaSuccess;
     if (c.cm_mode != 4 || c.fwd == nullptr) return cudaErrorInvalidValue;
-    if (c.ngaps > 0) {
-        dim3 g((unsigned)((c.ngaps + 256 * 8 - 1) / (256 * 8)), (unsigned)(nframes < 65535 ? nframes : 65535));
-        img_gap_fill_kernel<<<g, 256, 0, st>>>(d_img, c.gaps, c.ngaps, (size_t)c.H * c.W, nframes);
-    }
+    cudaError_t e = psr_launch_image_gap_fill(c, nframes, d_img, st);
+    if (e != cudaSuccess) return e;
     return launch_banks<true>(c, d_raw, nframes, d_img, st);
 }

@@ -283,6 +283,10 @@ def test_image_matches_scatter_last_writer_wins(torch, kind, nseg, cm):
     got = cal.calib(_to_dev(torch, raw), image=True).cpu().numpy()
     exp = np.stack([oc.det_image(spec.kind, raw[f], consts, iX, iY, cm) for f in range(2)])
     kat.assert_same_bits(got, exp, "image")
+    if cm is None:                                                     # the other raw -> image kernel (output-driven gather): same bits
+        cal.set_option("image_gather", 1)
+        kat.assert_same_bits(cal.calib(_to_dev(torch, raw), image=True).cpu().numpy(), exp, "image, gather kernel")
+        cal.set_option("image_gather", 0)
     # producer masks act on the 2-D image (ref: producer.py:92-97), not on the calib layout
     rng = np.random.default_rng(62)
     keep = rng.random((H, W)) > 0.3
@@ -291,6 +295,9 @@ def test_image_matches_scatter_last_writer_wins(torch, kind, nseg, cm):
     got = cal.calib(_to_dev(torch, raw), image=True).cpu().numpy()
     exp_k = np.concatenate([oc.producer_masks(exp[f], None, keep) for f in range(2)])
     kat.assert_same_bits(got, exp_k, "image + keep")
+    if cm is None:
+        cal.set_option("image_gather", 1)
+        kat.assert_same_bits(cal.calib(_to_dev(torch, raw), image=True).cpu().numpy(), exp_k, "image + keep, gather kernel")
 
 
 def test_image_width_not_multiple_of_4(torch):

@@ -24,6 +24,8 @@ ap.add_argument("--out", default=None)
 ap.add_argument("--cm-mode", type=int, default=4)
 ap.add_argument("--det", default=None)
 ap.add_argument("--npix-min", type=int, default=10)
+ap.add_argument("--gap", type=int, default=10, help="panel gap of the synthetic geometry (image width = f(gap): 10 -> W % 4 == 2, 12 -> W % 4 == 0)")
+ap.add_argument("--opt", action="append", default=[], help="name=value for psr_set_option, e.g. image_gather=1")
 a = ap.parse_args()
 
 det = a.det or ("jungfrau4M" if a.workload == "jungfrau" else "epix10k2M")
@@ -32,7 +34,7 @@ consts = syn.make_constants(spec, seed=0)
 raw = syn.make_raw_frames(spec, consts, 8, seed=1)
 raw = np.concatenate([raw] * (a.batch // 8))
 d_raw = torch.from_numpy(raw.view(np.int16)).cuda()
-geo = syn.make_pixel_index_arrays(spec) if a.workload == "image_nocm" else None
+geo = syn.make_pixel_index_arrays(spec, gap=a.gap) if a.workload == "image_nocm" else None
 peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
 libs = []
 for pat in a.libs:
@@ -52,6 +54,8 @@ for path in libs:
     if geo is not None:
         assert lib.psr_set_geometry(ctx, p(geo[0]), p(geo[1])) == 0
         H, W = C.c_int(), C.c_int(); lib.psr_image_shape(ctx, C.byref(H), C.byref(W)); nout = H.value * W.value; out_kind = 1
+    for kv in a.opt:
+        k, v = kv.split("="); assert lib.psr_set_option(ctx, k.encode(), int(v)) == 0, lib.psr_last_error()
     d_out = torch.empty((a.batch, nout), dtype=torch.float32, device="cuda")
     alg = (2 * spec.npix + 4 * nout) * a.batch
     st = torch.cuda.current_stream().cuda_stream
