@@ -468,8 +468,7 @@ image_fused_kernel(const uint16_t* __restrict__ raw, float* __restrict__ img, Ps
 // owns 4 pixels, holds their constants in registers and walks the frames of the batch -- with the image
 // index of every owned pixel (PsrDev::fwd, the scatter side of the geometry) held in registers too, so
 // the calibrated values go straight to their places: 12 + ~3 thread-instructions per pixel against 36 for
-// the output-driven gather.  Four CTAs share a tile of 32 rows x 128 pixels; which quarter a CTA takes and which
-// pixels of it a warp owns depends on how the tile lies in the image (see `rot` below), so that stores cover whole image-row pieces either way.
+// the output-driven gather.  Which pixels a CTA and its warps own depends on how the segment lies in the image (see `rot` below), so that stores cover whole image-row pieces either way.
 // Neighbouring CTAs run concurrently on neighbouring tiles and the same frames, so sectors shared across a
 // tile border are completed in L2.  Gaps are zeroed by psr_launch_image_gap_fill.
 // =================================================================================================
@@ -480,9 +479,18 @@ image_fused_kernel(const uint16_t* __restrict__ raw, float* __restrict__ img, Ps
 #define PSR_IMGS_MINB 3
 #endif
 
+#ifndef PSR_IMGS_ROT_ST      /* scattered stores: 0 = .cs (evict-first), 1 = plain write-back */
+#define PSR_IMGS_ROT_ST 1
+#endif
+// Scattered stores leave partly written sectors at tile borders until the neighbouring CTA writes the rest; evicted
+// early (evict-first) they cost a read-modify-write in DRAM, so these stores keep the normal eviction priority.
 __device__ __forceinline__ void imgs_st_at(float* base, int32_t t, float v)
 {
+#if PSR_IMGS_ROT_ST == 0
     asm volatile("{ .reg .u64 a; mad.wide.u32 a, %1, 4, %0; st.global.cs.f32 [a], %2; }" :: "l"(base), "r"(t), "f"(v) : "memory");
+#else
+    asm volatile("{ .reg .u64 a; mad.wide.u32 a, %1, 4, %0; st.global.f32 [a], %2; }" :: "l"(base), "r"(t), "f"(v) : "memory");
+#endif
 }
 
 // 4 consecutive floats at any 4-byte alignment
@@ -492,7 +500,7 @@ __device__ __forceinline__ void imgs_store_run4(float* p, float o0, float o1, fl
     if (a == 0)      { __stcs(reinterpret_cast<float4*>(p), make_float4(o0, o1, o2, o3)); }
     else if (a == 2) { __stcs(reinterpret_cast<float2*>(p), make_float2(o0, o1)); __stcs(reinterpret_cast<float2*>(p + 2), make_float2(o2, o3)); }
     else if (a == 1) { __stcs(p, o0); __stcs(reinterpret_cast<float2*>(p + 1), make_float2(o1, o2)); __stcs(p + 3, o3); }
-    else             { __stcs(p, o0); __stcs(p + 1, o1); __stcs(reinterpret_cast<float2*>(p + 2), make_float2(o2, o3)); }
+    else             { __stcs(p, o0); __stcs(reinterpret_cast<float2*>(p + 1), make_float2(o1, o2)); __stcs(p + 3, o3); }    // a == 3: p + 1 is 16-byte aligned
 }
 
 template <int DET, bool HAS_OFFS>
@@ -500,28 +508,31 @@ __global__ void __launch_bounds__(256, PSR_IMGS_MINB)
 image_scatter_kernel(const uint2* __restrict__ raw, float* __restrict__ img, PsrDev c, int nframes, int fpb)
 {
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const int tiles_x = c.cols / 128, tiles_y = c.rows / 32;
-    int b = blockIdx.x;
-    const int tx = b % tiles_x; b /= tiles_x;
-    const int ty = b % tiles_y; const int seg = b / tiles_y;
-    const int pass = blockIdx.y & 3;                   // quarter of the 32 x 128 tile this CTA takes
-    const int ngroups = c.npix / 4;
-    // Which way the tile lies in the image decides who owns what (a speed matter only: any ownership is correct).
-    // Unrotated / 180 degrees: the CTA takes 8 rows of the tile, a warp one row of 128 pixels -- exactly the calib map
-    // kernel's pattern: 256 contiguous bytes of raw and 512 contiguous bytes of image per warp instruction.
-    // Rotated by 90 / 270 degrees (detector rows run along image columns): the CTA takes 32 columns of the tile, a warp
-    // 4 pixels of 32 consecutive ROWS, so each of its four scalar stores is 32 consecutive floats of one image row; the
-    // 8-byte raw loads of a warp then touch 32 sectors a quarter each, and the other three quarters are what the CTA's
-    // neighbouring warps load -- those loads go through L1 instead of streaming past it.
+    const int ngroups = c.npix / 4, gps = ngroups / c.nseg;              // 4-pixel groups in the batch frame / in a segment
+    const int bps = gps / 256;                                           // CTAs per segment (256 groups each)
+    const int seg = blockIdx.x / bps, lb = blockIdx.x - seg * bps;
+    // How the segment lies in the image decides who owns what (a speed matter only: any ownership is correct).
+    // Unrotated / 180 degrees: the calib map kernel's ownership -- the CTA takes 1024 consecutive pixels, a warp 128 of them:
+    // 256 contiguous bytes of raw and 512 contiguous bytes of image per warp instruction, whole detector rows per CTA.
+    // Rotated by 90 / 270 degrees (detector rows run along image columns): four CTAs share a tile of 32 rows x 128 pixels, each
+    // takes 32 columns of it and a warp 4 pixels of 32 consecutive ROWS, so each of its four scalar stores is 32 consecutive
+    // floats of one image row; the 8-byte raw loads of a warp then touch 32 sectors a quarter each (the CTA's other warps use
+    // the rest; loaded through L1).  Measured: 2.4x the L2 reads and 1.9x the DRAM reads of the unrotated pattern -- and still
+    // faster than loading row-wise and exchanging through shared memory (319 vs 291 us on an all-rotated geometry).
     bool rot;
     {
-        const int4 pt = __ldg(reinterpret_cast<const int4*>(c.fwd) + (((seg * c.rows + ty * 32) * c.cols + tx * 128) >> 2));
+        const int4 pt = __ldg(reinterpret_cast<const int4*>(c.fwd) + (size_t)seg * gps + (gps >> 1));     // a group in the middle of the segment
         const int d = pt.y - pt.x;
         rot = pt.x >= 0 && pt.y >= 0 && d != 1 && d != -1;
     }
-    const int row = ty * 32 + (rot ? lane : pass * 8 + w);
-    const int col = tx * 128 + (rot ? pass * 32 + w * 4 : lane * 4);
-    const int g = ((seg * c.rows + row) * c.cols + col) >> 2;
+    int g;
+    if (rot) {
+        const int tiles_x = c.cols / 128, t = lb >> 2, pass = lb & 3;
+        const int ty = t / tiles_x, tx = t - ty * tiles_x;
+        g = ((seg * c.rows + ty * 32 + lane) * c.cols + tx * 128 + pass * 32 + w * 4) >> 2;
+    } else {
+        g = seg * gps + lb * 256 + tid;
+    }
     const size_t fimg = (size_t)c.H * c.W;
 
     // per-run constants of the 4 owned pixels, in registers for the whole batch
@@ -551,7 +562,7 @@ image_scatter_kernel(const uint2* __restrict__ raw, float* __restrict__ img, Psr
     const bool desc = all && t[1] == t[0] - 1 && t[2] == t[0] - 2 && t[3] == t[0] - 3;
     const int kind = asc ? 1 : desc ? 2 : all ? 3 : 0;
 
-    const int f_begin = (blockIdx.y >> 2) * fpb, f_end = min(nframes, f_begin + fpb);
+    const int f_begin = blockIdx.y * fpb, f_end = min(nframes, f_begin + fpb);
     auto frames = [&](int f, auto nconst) {
         constexpr int NF = decltype(nconst)::value;
         uint2 r[NF];
@@ -572,6 +583,9 @@ image_scatter_kernel(const uint2* __restrict__ raw, float* __restrict__ img, Psr
                 o[3] = jf_px<HAS_OFFS>(r[u].y >> 16,     P[3], O[3], G[3], fl >> 24);
             }
             float* imgf = img + (size_t)(f + u) * fimg;
+#ifdef PSR_IMGS_HACK   /* timing experiment only: wrong unless every run is ascending and 16-byte aligned */
+            __stcs(reinterpret_cast<float4*>(imgf + t[0]), make_float4(o[0], o[1], o[2], o[3])); continue;
+#endif
             if (kind == 1) imgs_store_run4(imgf + t[0], o[0], o[1], o[2], o[3]);
             else if (kind == 2) imgs_store_run4(imgf + t[3], o[3], o[2], o[1], o[0]);
             else if (kind == 3) {
@@ -716,7 +730,7 @@ cudaError_t psr_launch_image_scatter(const PsrDev& c, const uint16_t* d_raw, int
     cudaError_t e = psr_launch_image_gap_fill(c, nframes, d_img, st);
     if (e != cudaSuccess) return e;
     if (fpb <= 0 || fpb > nframes) fpb = nframes > 64 ? 64 : nframes;
-    dim3 grid((unsigned)(c.nseg * (c.rows / 32) * (c.cols / 128)), 4u * (unsigned)((nframes + fpb - 1) / fpb));
+    dim3 grid((unsigned)(c.npix / 1024), (unsigned)((nframes + fpb - 1) / fpb));       // rows % 32 == 0 and cols % 128 == 0: a segment is a whole number of CTAs
     const uint2* r = reinterpret_cast<const uint2*>(d_raw);
     if (c.det_kind == 0) image_scatter_kernel<0, false><<<grid, 256, 0, st>>>(r, d_img, c, nframes, fpb);
     else if (c.offs != nullptr) image_scatter_kernel<1, true><<<grid, 256, 0, st>>>(r, d_img, c, nframes, fpb);

@@ -696,7 +696,7 @@ __device__ __forceinline__ void img_store_run(float* p, const float (&o)[8])
         if (a == 0)      { __stcs(reinterpret_cast<float4*>(p), make_float4(o[0], o[1], o[2], o[3])); }
         else if (a == 2) { __stcs(reinterpret_cast<float2*>(p), make_float2(o[0], o[1])); __stcs(reinterpret_cast<float2*>(p + 2), make_float2(o[2], o[3])); }
         else if (a == 1) { __stcs(p, o[0]); __stcs(reinterpret_cast<float2*>(p + 1), make_float2(o[1], o[2])); __stcs(p + 3, o[3]); }
-        else             { __stcs(p, o[0]); __stcs(p + 1, o[1]); __stcs(reinterpret_cast<float2*>(p + 2), make_float2(o[2], o[3])); }
+        else             { __stcs(p, o[0]); __stcs(reinterpret_cast<float2*>(p + 1), make_float2(o[1], o[2])); __stcs(p + 3, o[3]); }
     }
 }
 

@@ -343,23 +343,23 @@ def test_bank_common_mode_fused_with_image_assembly(torch, kind, nseg, nframes):
 
 @pytest.mark.parametrize("shift", [0, 1, 2, 3])
 def test_fused_image_runs_at_every_store_alignment(torch, shift):
-    """Identity geometry shifted by 0..3 columns in an image 389 wide: ascending runs start at every 4-byte alignment."""
+    """Identity geometry shifted by 0..3 columns in an image up to 389 wide: runs start at every 4-byte alignment, in
+    the common-mode kernel's image epilogue and in the scatter kernel (one pixel sent elsewhere breaks a chain of runs)."""
     spec = syn.EPIX10K2M.with_nseg(1)
     consts = syn.make_constants(spec, seed=68)
     raw = syn.make_raw_frames(spec, consts, 2, seed=69)
     r, c = np.meshgrid(np.arange(spec.rows), np.arange(spec.cols), indexing="ij")
     iX = (r[None] + 1).astype(np.int32); iY = (c[None] + shift).astype(np.int32)
     iY[0, -1, -1] = 388                                                   # fixes W = 389 (odd) for every shift
-    cm = (7, 4, 50.0, 10)
-    for flip in (False, True):                                            # flipped: descending runs (panel rotated by 180)
-        jY = (388 - iY).astype(np.int32) if flip else iY
+    for flip, cm in [(False, (7, 4, 50.0, 10)), (True, (7, 4, 50.0, 10)), (False, None), (True, None)]:   # flipped: descending runs (180 degrees)
+        jY = (388 - iY).astype(np.int32) if flip else iY                 # cm None: the scatter kernel's shuffle-realigned stores
         cal = _calibrator(spec, consts)
         cal.set_common_mode(cm)
         assert cal.set_geometry(iX, jY) == (353, int(jY.max()) + 1)
         out = torch.full(cal.out_shape(2, True), float("nan"), device="cuda")
         cal.calib(_to_dev(torch, raw), out=out, image=True)
         exp = np.stack([oc.det_image(spec.kind, raw[f], consts, iX, jY, cm) for f in range(2)])
-        kat.assert_same_bits(out.cpu().numpy().reshape(exp.shape), exp, f"shift {shift} flip {flip}")
+        kat.assert_same_bits(out.cpu().numpy().reshape(exp.shape), exp, f"shift {shift} flip {flip} cm {cm}")
 
 
 # ---- host-fed pipeline, edge cases, errors ---------------------------------------------------------------
