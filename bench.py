@@ -293,7 +293,7 @@ def main():
     d_out = torch.empty(cal.out_shape(B, image), dtype=torch.float32, device="cuda")
     h_out = torch.empty(cal.out_shape(B, image), dtype=torch.float32).pin_memory()
     stream = torch.cuda.current_stream()
-    launches_per_step = 2 if (image and cmpars is not None) else 1
+    launches_per_step = 2 if image else 1           # image modes: the scatter / common-mode kernel + the gap-fill kernel beside it
 
     # ---- device-resident throughput ---------------------------------------------------------------
     sampler = ClockSampler(dev)

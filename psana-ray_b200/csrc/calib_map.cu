@@ -473,7 +473,7 @@ image_fused_kernel(const uint16_t* __restrict__ raw, float* __restrict__ img, Ps
 // tile border are completed in L2.  Gaps are zeroed by psr_launch_image_gap_fill.
 // =================================================================================================
 #ifndef PSR_IMGS_UNROLL
-#define PSR_IMGS_UNROLL 4
+#define PSR_IMGS_UNROLL 8
 #endif
 #ifndef PSR_IMGS_MINB
 #define PSR_IMGS_MINB 3
@@ -583,9 +583,6 @@ image_scatter_kernel(const uint2* __restrict__ raw, float* __restrict__ img, Psr
                 o[3] = jf_px<HAS_OFFS>(r[u].y >> 16,     P[3], O[3], G[3], fl >> 24);
             }
             float* imgf = img + (size_t)(f + u) * fimg;
-#ifdef PSR_IMGS_HACK   /* timing experiment only: wrong unless every run is ascending and 16-byte aligned */
-            __stcs(reinterpret_cast<float4*>(imgf + t[0]), make_float4(o[0], o[1], o[2], o[3])); continue;
-#endif
             if (kind == 1) imgs_store_run4(imgf + t[0], o[0], o[1], o[2], o[3]);
             else if (kind == 2) imgs_store_run4(imgf + t[3], o[3], o[2], o[1], o[0]);
             else if (kind == 3) {
@@ -727,8 +724,6 @@ cudaError_t psr_launch_image_scatter(const PsrDev& c, const uint16_t* d_raw, int
 {
     if (nframes <= 0) return cudaSuccess;
     if (c.fwd == nullptr || c.rows % 32 != 0 || c.cols % 128 != 0) return cudaErrorInvalidValue;
-    cudaError_t e = psr_launch_image_gap_fill(c, nframes, d_img, st);
-    if (e != cudaSuccess) return e;
     if (fpb <= 0 || fpb > nframes) fpb = nframes > 64 ? 64 : nframes;
     dim3 grid((unsigned)(c.npix / 1024), (unsigned)((nframes + fpb - 1) / fpb));       // rows % 32 == 0 and cols % 128 == 0: a segment is a whole number of CTAs
     const uint2* r = reinterpret_cast<const uint2*>(d_raw);

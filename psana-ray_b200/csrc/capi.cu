@@ -86,6 +86,7 @@ struct psr_ctx {
     std::vector<int32_t> h_fwd;                               // per source pixel: winning image index or INT32_MIN, before the image keep mask
     uint8_t* d_keep_image = nullptr;
     float* d_scratch = nullptr; size_t scratch_elems = 0;
+    cudaStream_t s_gap = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr;    // gap fill runs beside the scatter kernels
     int image_gather = 0;          // 1: raw -> image through the output-driven gather kernel instead of the scatter kernel
     int frames_per_block = 0;      // 0 = auto: persistent balanced schedule; > 0 forces the (tile, frame chunk) grid
     HostPipe pipe;
@@ -150,6 +151,27 @@ int ensure_scratch(psr_ctx* c, size_t elems) {
     return PSR_OK;
 }
 
+// Zero the image pixels no detector pixel maps to, on a side stream forked from `st`: the scatter kernels write the
+// other pixels, so the two need no order between them, only both after what `st` held before and both before what follows.
+int gap_fill_fork(psr_ctx* c, int nframes, float* d_img, cudaStream_t st) {
+    if (c->dev.ngaps <= 0) return PSR_OK;
+    if (!c->s_gap) {
+        PSR_CUDA(cudaStreamCreateWithFlags(&c->s_gap, cudaStreamNonBlocking));
+        PSR_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+        PSR_CUDA(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
+    }
+    PSR_CUDA(cudaEventRecord(c->ev_fork, st));
+    PSR_CUDA(cudaStreamWaitEvent(c->s_gap, c->ev_fork, 0));
+    PSR_CUDA(psr_launch_image_gap_fill(c->dev, nframes, d_img, c->s_gap));
+    PSR_CUDA(cudaEventRecord(c->ev_join, c->s_gap));
+    return PSR_OK;
+}
+int gap_fill_join(psr_ctx* c, cudaStream_t st) {
+    if (c->dev.ngaps <= 0) return PSR_OK;
+    PSR_CUDA(cudaStreamWaitEvent(st, c->ev_join, 0));
+    return PSR_OK;
+}
+
 int launch_batch(psr_ctx* c, const uint16_t* d_raw, int nframes, float* d_out, int out_kind, cudaStream_t st) {
     const PsrDev& d = c->dev;
     const int fpb = c->frames_per_block;      // 0 = persistent balanced schedule (map kernels); image gather: whole batch per CTA
@@ -158,12 +180,21 @@ int launch_batch(psr_ctx* c, const uint16_t* d_raw, int nframes, float* d_out, i
         else                PSR_CUDA(psr_launch_common_mode(d, d_raw, nframes, d_out, st));
     } else {
         if (d.cm_mode == 0) {
-            if (d.fwd != nullptr && !c->image_gather) PSR_CUDA(psr_launch_image_scatter(d, d_raw, nframes, d_out, fpb, st));
-            else PSR_CUDA(psr_launch_image_fused(d, d_raw, nframes, d_out, fpb, st));
+            if (d.fwd != nullptr && !c->image_gather) {
+                int rc = gap_fill_fork(c, nframes, d_out, st);
+                if (rc != PSR_OK) return rc;
+                PSR_CUDA(psr_launch_image_scatter(d, d_raw, nframes, d_out, fpb, st));
+                rc = gap_fill_join(c, st);
+                if (rc != PSR_OK) return rc;
+            } else PSR_CUDA(psr_launch_image_fused(d, d_raw, nframes, d_out, fpb, st));
         } else if (d.cm_mode == 4 && d.fwd != nullptr) {
             // bank medians only: the common-mode kernel writes each tile straight into the images (no scratch, no second pass)
             PsrDev t = d; t.ignore_keep = 1;
+            int rc = gap_fill_fork(c, nframes, d_out, st);
+            if (rc != PSR_OK) return rc;
             PSR_CUDA(psr_launch_common_mode_image(t, d_raw, nframes, d_out, st));
+            rc = gap_fill_join(c, st);
+            if (rc != PSR_OK) return rc;
         } else {
             int rc = ensure_scratch(c, (size_t)nframes * d.npix);
             if (rc != PSR_OK) return rc;
@@ -238,6 +269,9 @@ void psr_destroy(psr_ctx* c) {
     if (c->pipe.s_in) cudaStreamDestroy(c->pipe.s_in);
     if (c->pipe.s_comp) cudaStreamDestroy(c->pipe.s_comp);
     if (c->pipe.s_out) cudaStreamDestroy(c->pipe.s_out);
+    if (c->s_gap) cudaStreamDestroy(c->s_gap);
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
     if (c->d_consts) cudaFree(c->d_consts);
     if (c->d_flags) cudaFree(c->d_flags);
     if (c->d_inv) cudaFree(c->d_inv);

@@ -1073,7 +1073,5 @@ cudaError_t psr_launch_common_mode_image(const PsrDev& c, const uint16_t* d_raw,
 {
     if (nframes <= 0) return cudaSuccess;
     if (c.cm_mode != 4 || c.fwd == nullptr) return cudaErrorInvalidValue;
-    cudaError_t e = psr_launch_image_gap_fill(c, nframes, d_img, st);
-    if (e != cudaSuccess) return e;
     return launch_banks<true>(c, d_raw, nframes, d_img, st);
 }

@@ -41,13 +41,14 @@ cudaError_t psr_launch_calib_map(const PsrDev& c, const uint16_t* d_raw, int nfr
 cudaError_t psr_launch_decode(const PsrDev& c, const uint16_t* d_raw, int nframes, uint8_t* d_modes, cudaStream_t st);
 cudaError_t psr_launch_image_fused(const PsrDev& c, const uint16_t* d_raw, int nframes, float* d_img,
                                    int frames_per_block, cudaStream_t st);
-// raw -> image by scatter through c.fwd (needs c.fwd / c.gaps); zero-fills the gaps first
+// raw -> image by scatter through c.fwd; writes every image pixel some detector pixel maps to -- the caller zeroes the
+// rest with psr_launch_image_gap_fill (any order, any stream: the two write disjoint pixels)
 cudaError_t psr_launch_image_scatter(const PsrDev& c, const uint16_t* d_raw, int nframes, float* d_img,
                                      int frames_per_block, cudaStream_t st);
 cudaError_t psr_launch_image_gap_fill(const PsrDev& c, int nframes, float* d_img, cudaStream_t st);
 cudaError_t psr_launch_image_gather(const PsrDev& c, const float* d_calib, int nframes, float* d_img, cudaStream_t st);
 cudaError_t psr_launch_common_mode(const PsrDev& c, const uint16_t* d_raw, int nframes, float* d_out, cudaStream_t st);
-// common mode + image assembly in one pass (bank medians only: cm_mode == 4; needs c.fwd / c.gaps)
+// common mode + image assembly in one pass (bank medians only: cm_mode == 4; needs c.fwd); gaps as above
 cudaError_t psr_launch_common_mode_image(const PsrDev& c, const uint16_t* d_raw, int nframes, float* d_img, cudaStream_t st);
 cudaError_t psr_common_mode_setup(void);   // raises the dynamic shared-memory limit once per device
 
