@@ -476,11 +476,16 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     __shared__ int selsh[40];
 
     const int tid = threadIdx.x, lane = tid & 31;
+    // Block order: bank fastest, then FRAME, then (half, segment).  The CTAs resident at one time then work on all frames of
+    // a few half-segments, so the tiles' constants are fetched from DRAM once per batch and come from L2 for the other frames
+    // (Jungfrau: 155 MB of constants do not fit L2; with the frame slowest they were re-read for every frame -- ncu: 10.5 GB of
+    // DRAM reads per 64 frames), while the banks of one frame's row band still run side by side (whole rows of raw and output).
     int bid = blockIdx.x;
+    const int nframes = (int)(gridDim.x / (unsigned)(c.nseg * 2 * NB));
     const int bank = bid % NB; bid /= NB;
-    const int half = bid & 1;  bid >>= 1;
-    const int seg = bid % c.nseg;
-    const int frame = bid / c.nseg;
+    const int frame = bid % nframes; bid /= nframes;
+    const int half = bid & 1;
+    const int seg = bid >> 1;
     const uint16_t* rawf = raw + (size_t)frame * c.npix;
     float* outf = out + (size_t)frame * c.npix;
     const int mode = c.cm_mode;
@@ -770,11 +775,16 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     __shared__ int selsh[40];
 
     const int tid = threadIdx.x;
+    // Block order: bank fastest, then FRAME, then (half, segment).  The CTAs resident at one time then work on all frames of
+    // a few half-segments, so the tiles' constants are fetched from DRAM once per batch and come from L2 for the other frames
+    // (Jungfrau: 155 MB of constants do not fit L2; with the frame slowest they were re-read for every frame -- ncu: 10.5 GB of
+    // DRAM reads per 64 frames), while the banks of one frame's row band still run side by side (whole rows of raw and output).
     int bid = blockIdx.x;
+    const int nframes = (int)(gridDim.x / (unsigned)(c.nseg * 2 * NB));
     const int bank = bid % NB; bid /= NB;
-    const int half = bid & 1;  bid >>= 1;
-    const int seg = bid % c.nseg;
-    const int frame = bid / c.nseg;
+    const int frame = bid % nframes; bid /= nframes;
+    const int half = bid & 1;
+    const int seg = bid >> 1;
     const uint16_t* rawf = raw + (size_t)frame * c.npix;
     float* outf = out + (size_t)frame * (IMG ? (size_t)c.H * c.W : (size_t)c.npix);    // IMG: out is the batch of assembled images
 
@@ -794,8 +804,10 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
         float pa[8], pb[8], pc[8], oa[8], ob[8], oc[8];
         if (DET == 0) { ldN<CW>(c.ped0 + gp, pa); ldN<CW>(c.ped1 + gp, pb); }
         else {
-            ldN<CW>(c.peds + gp, pa); ldN<CW>(c.peds + c.npix + gp, pb); ldN<CW>(c.peds + 2 * (size_t)c.npix + gp, pc);
-            if (c.offs != nullptr) { ldN<CW>(c.offs + gp, oa); ldN<CW>(c.offs + c.npix + gp, ob); ldN<CW>(c.offs + 2 * (size_t)c.npix + gp, oc); }
+            ldN<CW>(c.peds + gp, pa);
+            if (c.offs != nullptr) ldN<CW>(c.offs + gp, oa);
+            ldN<CW>(c.peds + c.npix + gp, pb); ldN<CW>(c.peds + 2 * (size_t)c.npix + gp, pc);
+            if (c.offs != nullptr) { ldN<CW>(c.offs + c.npix + gp, ob); ldN<CW>(c.offs + 2 * (size_t)c.npix + gp, oc); }
         }
 #pragma unroll
         for (int i = 0; i < CW; ++i) {
@@ -845,7 +857,10 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
         const int gp = ((seg * ROWS + half * TR + r) * COLS) + bank * TC + cc * CW;
         float ga[8], gb_[8], gc[8];
         if (DET == 0) { ldN<CW>(c.gf0 + gp, ga); ldN<CW>(c.gf1 + gp, gb_); }
-        else { ldN<CW>(c.gfac + gp, ga); ldN<CW>(c.gfac + c.npix + gp, gb_); ldN<CW>(c.gfac + 2 * (size_t)c.npix + gp, gc); }
+        else {
+            ldN<CW>(c.gfac + gp, ga);
+            ldN<CW>(c.gfac + c.npix + gp, gb_); ldN<CW>(c.gfac + 2 * (size_t)c.npix + gp, gc);
+        }
         uint32_t fw[2];
         ld_flags<CW>(c.flags + gp, fw);                                              // L1/L2 hit: read in the load phase
         float o[8];
