@@ -510,7 +510,10 @@ image_scatter_kernel(const uint2* __restrict__ raw, float* __restrict__ img, Psr
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const int ngroups = c.npix / 4, gps = ngroups / c.nseg;              // 4-pixel groups in the batch frame / in a segment
     const int bps = gps / 256;                                           // CTAs per segment (256 groups each)
-    const int seg = blockIdx.x / bps, lb = blockIdx.x - seg * bps;
+    // blocks run in the order of their place in the IMAGE (PsrDev::blk_order): CTAs resident together then write neighbouring
+    // image rows, whichever segments those come from, instead of half-filling DRAM pages that another segment completes later
+    const int blk = c.blk_order != nullptr ? __ldg(c.blk_order + blockIdx.x) : (int)blockIdx.x;
+    const int seg = blk / bps, lb = blk - seg * bps;
     // How the segment lies in the image decides who owns what (a speed matter only: any ownership is correct).
     // Unrotated / 180 degrees: the calib map kernel's ownership -- the CTA takes 1024 consecutive pixels, a warp 128 of them:
     // 256 contiguous bytes of raw and 512 contiguous bytes of image per warp instruction, whole detector rows per CTA.

@@ -8,9 +8,11 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <mutex>
 #include <new>
 #include <string>
+#include <utility>
 #include <vector>
 
 // Scratch of psr_calib_image_noalloc: lives in the library image, so no call ever allocates it.
@@ -82,6 +84,7 @@ struct psr_ctx {
     void* d_consts = nullptr; size_t consts_bytes = 0;
     uint8_t* d_flags = nullptr;
     int32_t* d_inv = nullptr;
+    int32_t* d_blk_order = nullptr;
     int32_t* d_fwd = nullptr; int32_t* d_gaps = nullptr;     // scatter side of the geometry (common mode fused with assembly)
     std::vector<int32_t> h_fwd;                               // per source pixel: winning image index or INT32_MIN, before the image keep mask
     uint8_t* d_keep_image = nullptr;
@@ -277,6 +280,7 @@ void psr_destroy(psr_ctx* c) {
     if (c->d_inv) cudaFree(c->d_inv);
     if (c->d_fwd) cudaFree(c->d_fwd);
     if (c->d_gaps) cudaFree(c->d_gaps);
+    if (c->d_blk_order) cudaFree(c->d_blk_order);
     if (c->d_keep_image) cudaFree(c->d_keep_image);
     if (c->d_scratch) cudaFree(c->d_scratch);
     delete c;
@@ -378,7 +382,8 @@ int psr_set_geometry(psr_ctx* c, const int32_t* h_iX, const int32_t* h_iY) {
         PSR_CUDA(cudaMalloc(&c->d_inv, inv.size() * sizeof(int32_t)));
         PSR_CUDA(cudaMemcpy(c->d_inv, inv.data(), inv.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
         // scatter side: every source pixel that is the last writer of its target stores there, nobody else does
-        c->dev.fwd = nullptr; c->dev.gaps = nullptr; c->dev.ngaps = 0;
+        c->dev.fwd = nullptr; c->dev.gaps = nullptr; c->dev.ngaps = 0; c->dev.blk_order = nullptr;
+        if (c->d_blk_order) { PSR_CUDA(cudaFree(c->d_blk_order)); c->d_blk_order = nullptr; }
         if (c->d_fwd) { PSR_CUDA(cudaFree(c->d_fwd)); c->d_fwd = nullptr; }
         if (c->d_gaps) { PSR_CUDA(cudaFree(c->d_gaps)); c->d_gaps = nullptr; }
         c->h_fwd.assign(n, INT32_MIN);
@@ -395,6 +400,37 @@ int psr_set_geometry(psr_ctx* c, const int32_t* h_iX, const int32_t* h_iY) {
         int rc = upload_fwd(c, nullptr);
         if (rc != PSR_OK) return rc;
         c->dev.gaps = c->d_gaps; c->dev.ngaps = (int)gaps.size();
+        if (c->dev.rows % 32 == 0 && c->dev.cols % 128 == 0) {
+            // launch order of the scatter kernel's 1024-pixel blocks: by image position of the block's first pixel that has a
+            // target.  Mirrors the kernel's block -> pixel rule (image_scatter_kernel): linear blocks on unrotated segments,
+            // quarter tiles of 32 rows x 128 pixels on segments rotated by 90/270 degrees.
+            const int rows = c->dev.rows, cols = c->dev.cols, pps = rows * cols, bps = pps / 1024, nblk = c->dev.nseg * bps;
+            std::vector<std::pair<int64_t, int32_t>> key((size_t)nblk);
+            for (int seg = 0; seg < c->dev.nseg; ++seg) {
+                const size_t probe = (size_t)seg * pps + (size_t)(pps / 8) * 4;          // group in the middle of the segment
+                const int32_t p0 = c->h_fwd[probe], p1 = c->h_fwd[probe + 1];
+                const bool rot = p0 >= 0 && p1 >= 0 && p1 - p0 != 1 && p1 - p0 != -1;
+                for (int lb = 0; lb < bps; ++lb) {
+                    int64_t best = INT64_MAX;
+                    for (int k = 0; k < 1024 && best == INT64_MAX; ++k) {                 // usually the very first pixel
+                        size_t px;
+                        if (!rot) px = (size_t)seg * pps + (size_t)lb * 1024 + k;
+                        else {
+                            const int tiles_x = cols / 128, t = lb >> 2, pass = lb & 3, ty = t / tiles_x, tx = t - ty * tiles_x;
+                            px = (size_t)seg * pps + (size_t)(ty * 32 + k / 32) * cols + tx * 128 + pass * 32 + k % 32;
+                        }
+                        if (c->h_fwd[px] >= 0) best = c->h_fwd[px];
+                    }
+                    key[(size_t)seg * bps + lb] = {best, (int32_t)(seg * bps + lb)};
+                }
+            }
+            std::sort(key.begin(), key.end());
+            std::vector<int32_t> order((size_t)nblk);
+            for (int i = 0; i < nblk; ++i) order[i] = key[i].second;
+            PSR_CUDA(cudaMalloc(&c->d_blk_order, order.size() * sizeof(int32_t)));
+            PSR_CUDA(cudaMemcpy(c->d_blk_order, order.data(), order.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+            c->dev.blk_order = c->d_blk_order;
+        }
     } catch (const std::bad_alloc&) { return fail(PSR_E_NOMEM, "out of host memory"); }
     c->dev.inv = c->d_inv; c->dev.H = H; c->dev.W = W;
     c->have_geometry = true;

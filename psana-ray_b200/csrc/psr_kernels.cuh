@@ -30,6 +30,7 @@ struct PsrDev {
     // last writer of that target (>= 0), ~index if the image keep mask zeroes that target, INT32_MIN if another
     // pixel wins the target; gaps = image indices no pixel maps to (they are zero-filled)
     const int32_t* fwd; const int32_t* gaps; int ngaps;
+    const int32_t* blk_order;      // scatter kernel: its 1024-pixel blocks sorted by where they land in the image (DRAM write locality), or null
     // common mode
     int cm_mode; float cormax; int npix_min; uint32_t elig_mask;
     int ignore_keep;               // 1: calib-layout keep mask not applied (image mode masks the 2-D image)
