@@ -50,6 +50,7 @@ class QueueServer:
             os.unlink(path)
         self.lsock = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
         self.lsock.bind(path + ".tmp")
+        os.chmod(path + ".tmp", 0o600)             # requests are pickles: only the owner may connect
         self.lsock.listen(256)
         os.rename(path + ".tmp", path)          # the name appears only once the server is listening
         self.lsock.setblocking(False)

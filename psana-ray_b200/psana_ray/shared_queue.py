@@ -227,7 +227,16 @@ def create_queue(queue_name="shared_queue", ray_namespace="default", maxsize=100
     """Start a detached queue server and return a handle, or ``None`` on failure (ref: shared_queue.py:33-38)."""
     try:
         path = socket_path(queue_name, ray_namespace, address)
-        os.makedirs(os.path.dirname(path), exist_ok=True)
+        # Messages are pickles, so whoever can connect can run code as the queue's owner (as with a Ray actor): the
+        # directories this call creates are private to the user, and the server makes the socket 0600.
+        d = os.path.dirname(path)
+        missing = []
+        while d and not os.path.isdir(d):
+            missing.append(d)
+            d = os.path.dirname(d)
+        os.makedirs(os.path.dirname(path), mode=0o700, exist_ok=True)
+        for m in missing:
+            os.chmod(m, 0o700)
         if os.path.exists(path):
             try:
                 QueueHandle(path).close()

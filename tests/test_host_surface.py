@@ -53,6 +53,17 @@ def test_inprocess_queue_contract():
     assert q.get_ex() == (True, None) and q.get_ex() == (False, None)
 
 
+def test_queue_socket_is_private_to_the_user(qroot):
+    """Requests are pickles, so connecting means running code as the owner: 0700 directories, 0600 socket."""
+    import stat
+    root, made = qroot
+    _mk(made, queue_name="priv", ray_namespace="nsp", maxsize=2)
+    path = SQ.socket_path("priv", "nsp")
+    assert stat.S_IMODE(os.stat(path).st_mode) == 0o600
+    assert stat.S_IMODE(os.stat(os.path.dirname(path)).st_mode) == 0o700
+    assert stat.S_IMODE(os.stat(root).st_mode) == 0o700
+
+
 def test_weighted_items_keep_maxsize_in_events():
     q = SQ.Queue(maxsize=100)
     assert q.put("a", 64) and not q.put("b", 64) and q.put("c", 36) and not q.put("d", 1)
