@@ -213,7 +213,7 @@ def reference_arm(args, rank, world):
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
     return 0
 
 
@@ -405,10 +405,22 @@ def main():
             "gpu_launches": args.steps * launches_per_step,
             "clocks": clocks,
         }
-        print(json.dumps(line), flush=True)
+        _emit(line)
     du.finalize()
     return 0
 
 
+def _emit(line):
+    """The JSON line goes to the process's ORIGINAL stdout; everything else written to fd 1 meanwhile (NCCL's version banner,
+    library chatter) was diverted to stderr, so stdout carries exactly one line."""
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_REAL_STDOUT, data)
+
+
+_REAL_STDOUT = 1
+
 if __name__ == "__main__":
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     sys.exit(main())

@@ -29,7 +29,7 @@ while True:
     except ValueError:
         if time.time() > t_deadline: raise
         time.sleep(0.05)
-n = 0; fb = 0; acc = torch.zeros((), dtype=torch.float64, device="cuda"); t_first = None
+n = 0; fb = 0; marks = []; acc = torch.zeros((), dtype=torch.float64, device="cuda"); t_first = None
 while True:
     b = rd.read_batch()
     if b is None:
@@ -38,9 +38,10 @@ while True:
     if t_first is None: t_first = time.time()
     acc += b[2].sum(dtype=torch.float64)          # the consumer really reads the frames
     n += b[2].shape[0]; fb = b[2][0].numel() * 4
+    marks.append((time.time(), n))
 torch.cuda.synchronize(); t_last = time.time()
 rd.close()
-print(json.dumps({"n": n, "t_first": t_first, "t_last": t_last, "sum": float(acc), "device": dev, "frame_bytes": fb}))
+print(json.dumps({"n": n, "t_first": t_first, "t_last": t_last, "sum": float(acc), "device": dev, "frame_bytes": fb, "marks": marks[::4]}))
 """
 
 
@@ -186,7 +187,7 @@ def main():
     ap.add_argument("--consumers", type=int, default=0)
     ap.add_argument("--events-per-rank", type=int, default=2048)
     ap.add_argument("--batch", type=int, default=64)
-    ap.add_argument("--queue-size", type=int, default=1024, help="events; 400 (the reference README) makes refused puts and their 0.1-2 s back-off dominate")
+    ap.add_argument("--queue-size", type=int, default=0, help="events; default 1024 per producer rank.  400 (the reference README) makes refused puts and their 0.1-2 s back-off dominate")
     ap.add_argument("--detector", default="epix10k2M")
     ap.add_argument("--image", action="store_true")
     ap.add_argument("--common-mode", default=None)
@@ -196,9 +197,11 @@ def main():
     if a.impl == "reference":
         if a.events_per_rank == 2048:
             a.events_per_rank = 300                # ~15-30 s of NumPy calibration
-        if a.queue_size == 1024:
+        if a.queue_size == 0:
             a.queue_size = 400                     # configs[0] / the reference README
         return reference_arm(a)
+    if a.queue_size == 0:
+        a.queue_size = 1024 * max(1, a.gpus)       # room for 16 batches per producer: a refused put costs a 0.1-2 s back-off
     if a.bridge:
         return bridge_arm(a)
     ncons = a.consumers or a.gpus
@@ -228,7 +231,17 @@ def main():
         stats = None
     total = sum(o["n"] for o in outs)
     t0 = min(o["t_first"] for o in outs if o["t_first"]); t1 = max(o["t_last"] for o in outs)
+    # steady state: the second half of the run (the first batches pay for CUDA-IPC mapping of every producer's slabs and for
+    # enabling peer access between every pair of GPUs)
+    tm = 0.5 * (t0 + t1)
+    def upto(o, t):
+        k = 0
+        for tt, nn in o.get("marks", []):
+            if tt <= t: k = nn
+        return k
+    steady = sum(o["n"] - upto(o, tm) for o in outs) / (t1 - tm)
     line = {"metric": "streamed calibrated frames/sec, producer -> queue -> consumer over CUDA IPC", "value": total / (t1 - t0), "unit": "frames/s",
+            "steady_state_value": steady,
             "n_gpus": a.gpus, "producers": a.gpus, "consumers": ncons, "events": total, "expected_events": nev, "seconds": t1 - t0,
             "per_consumer": [o["n"] for o in outs], "producer_exit_codes": rcs, "queue_stats": stats,
             "config": {"workload": "configs[4]: producer -> queue -> multi-consumer streaming, GPU-resident CUDA-IPC hand-off",

@@ -17,7 +17,6 @@ def init(backend: str, device=None):
     if world > 1 and not dist.is_initialized():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29500")
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # NCCL's version banner / debug lines must not land on stdout (one JSON line there)
         if device is not None:
             dist.init_process_group(backend, device_id=device)
         else:
