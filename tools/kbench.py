@@ -33,7 +33,7 @@ det = a.det or ("jungfrau4M" if a.workload == "jungfrau" else "epix10k2M")
 spec = syn.detector_spec(det)
 consts = syn.make_constants(spec, seed=0)
 raw = syn.make_raw_frames(spec, consts, 8, seed=1)
-raw = np.concatenate([raw] * (a.batch // 8))
+raw = np.concatenate([raw] * max(1, a.batch // 8))[:a.batch]
 d_raw = torch.from_numpy(raw.view(np.int16)).cuda()
 geo = syn.make_pixel_index_arrays(spec, gap=a.gap) if a.workload == "image_nocm" else None
 if geo is not None and a.geo != "default":
