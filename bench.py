@@ -264,6 +264,7 @@ def main():
     dev = local_rank % torch.cuda.device_count()
     torch.cuda.set_device(dev)
     from psana_ray import dist_util as du
+    numa_cpus = du.bind_to_gpu_numa(dev)              # before any pinned allocation: staging memory next to the GPU
     du.init("nccl", device=torch.device("cuda", dev))
 
     def barrier():
@@ -402,6 +403,7 @@ def main():
                     "host_out": {"value": e2e_host_value, "unit": "frames/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                                  "pcie_frac_of_63GBs_d2h": e2e_host_value / world * (d2h_bytes / B) / 1e9 / pcie_peak,
                                  "note": "whole calibrated batch copied back to pinned host memory, for a host-side consumer"}},
+            "numa_bind_cpus": (f"{numa_cpus[0]}-{numa_cpus[-1]} ({len(numa_cpus)})" if numa_cpus else None),
             "gpu_launches": args.steps * launches_per_step,
             "clocks": clocks,
         }

@@ -391,6 +391,10 @@ def main(argv=None):
         from . import _native
         _native.load()                                # fail loudly: there is no CPU fallback
         device = args.device if args.device is not None else world.local_rank % max(1, torch.cuda.device_count())
+        from .dist_util import bind_to_gpu_numa
+        cpus = bind_to_gpu_numa(device)              # pinned staging buffers are allocated below: first touch next to the GPU
+        if cpus:
+            logging.info(f"Rank {rank}: bound to CPUs {cpus[0]}-{cpus[-1]} next to cuda:{device}")
         bad = source.create_bad_pixel_mask() if args.uses_bad_pixel_mask else None
         manual = np.load(args.manual_mask_path) if args.manual_mask_path is not None else None
         nslabs = max(2, -(-args.queue_size // args.batch_size)) + 2
