@@ -58,3 +58,16 @@ def test_two_ranks_gloo_shard_without_collectives(tmp_path):
     for n in range(10):
         exp = float(np.float64(oc.det_calib("epix10ka", one.raw_event(n), one.constants()).sum(dtype=np.float64)))
         assert (s0 if n % 2 == 0 else s1)[n] == exp
+
+
+def test_numa_binding_is_a_no_op_without_nvml_or_when_disabled(monkeypatch):
+    """bind_to_gpu_numa must never fail a rank: no GPU / no NVML -> None and the affinity is untouched."""
+    import os
+    from psana_ray import dist_util as du
+    before = os.sched_getaffinity(0)
+    monkeypatch.setenv("PSANA_RAY_NO_NUMA_BIND", "1")
+    assert du.bind_to_gpu_numa(0) is None and os.sched_getaffinity(0) == before
+    monkeypatch.delenv("PSANA_RAY_NO_NUMA_BIND")
+    got = du.bind_to_gpu_numa(0)                      # here: no GPU, NVML init fails -> None
+    assert got is None or set(got) <= before
+    os.sched_setaffinity(0, before)
