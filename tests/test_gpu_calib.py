@@ -362,6 +362,32 @@ def test_fused_image_runs_at_every_store_alignment(torch, shift):
         kat.assert_same_bits(out.cpu().numpy().reshape(exp.shape), exp, f"shift {shift} flip {flip} cm {cm}")
 
 
+def test_constants_and_geometry_can_be_replaced_on_a_live_context(torch):
+    """A new run brings new constants / a new geometry: every derived table (2-entry constant table, flag bytes, inverse and
+    forward maps, gap list, block order, image keep mask) must be rebuilt, nothing of the old run may leak through."""
+    spec = syn.EPIX10K2M.with_nseg(4)
+    raw = None
+    cal = None
+    for seed, gap, cm in ((71, 10, None), (72, 7, (7, 4, 50.0, 10)), (73, 12, None)):
+        consts = syn.make_constants(spec, seed=seed, cfg_variant="mixed" if seed % 2 else "aml")
+        raw = syn.make_raw_frames(spec, consts, 2, seed=seed + 100)
+        iX, iY = syn.make_pixel_index_arrays(spec, gap=gap)
+        if cal is None:
+            cal = _calibrator(spec, consts)
+        else:
+            cal.set_constants(consts["peds"], consts.get("gain"), consts.get("offs"), consts.get("cfg"), consts.get("mask"))
+        cal.set_common_mode(cm)
+        H, W = cal.set_geometry(iX, iY)
+        keep = np.random.default_rng(seed).random((H, W)) > 0.1
+        cal.set_keep_mask(keep, image=True)
+        d = _to_dev(torch, raw)
+        kat.assert_same_bits(cal.calib(d).cpu().numpy(), _oracle_batch(spec, raw, consts, cm), f"calib, run {seed}")
+        exp = np.stack([oc.producer_masks(oc.det_image(spec.kind, raw[f], consts, iX, iY, cm), None, keep)[0] for f in range(2)])
+        out = torch.full(cal.out_shape(2, True), float("nan"), device="cuda")
+        cal.calib(d, out=out, image=True)
+        kat.assert_same_bits(out.cpu().numpy().reshape(exp.shape), exp, f"image, run {seed}")
+
+
 # ---- host-fed pipeline, edge cases, errors ---------------------------------------------------------------
 
 def test_host_pipeline_equals_device_path(torch):
