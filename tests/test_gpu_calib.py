@@ -388,6 +388,45 @@ def test_constants_and_geometry_can_be_replaced_on_a_live_context(torch):
         kat.assert_same_bits(out.cpu().numpy().reshape(exp.shape), exp, f"image, run {seed}")
 
 
+def test_two_contexts_two_threads_two_streams(torch):
+    """Contexts share nothing: an epix10ka and a Jungfrau calibrator driven from two host threads on two streams at once
+    (ctypes releases the GIL during the calls) give the oracle's bits every time, and each thread sees its own error string."""
+    import threading
+    from psana_ray import _native as N
+    jobs = []
+    for spec, seed, cm in ((syn.EPIX10K2M.with_nseg(4), 81, (7, 4, 50.0, 10)), (syn.JUNGFRAU4M.with_nseg(2), 82, (7, 7, 50.0, 10))):
+        consts = syn.make_constants(spec, seed=seed)
+        raw = syn.make_raw_frames(spec, consts, 3, seed=seed + 1)
+        cal = _calibrator(spec, consts)
+        cal.set_common_mode(cm)
+        jobs.append((spec, consts, raw, cal, cm, _oracle_batch(spec, raw, consts, cm)))
+    errors = []
+
+    def work(job, k):
+        spec, consts, raw, cal, cm, exp = job
+        try:
+            st = torch.cuda.Stream()
+            with torch.cuda.stream(st):
+                d = _to_dev(torch, raw)
+                for it in range(6):
+                    got = cal.calib(d)
+                    st.synchronize()
+                    kat.assert_same_bits(got.cpu().numpy(), exp, f"thread {k} iteration {it}")
+                try:                                           # an error in this thread only: wrong frame shape
+                    cal.calib(d[:, :1])
+                except ValueError:
+                    pass
+                lib = N.load()
+                rc = lib.psr_set_common_mode(cal._ctx, 99, 0.0, 0, 0)
+                assert rc != 0 and b"mode_bits = 99" in lib.psr_last_error()
+        except Exception as e:                                 # noqa: BLE001
+            errors.append((k, repr(e)))
+
+    ts = [threading.Thread(target=work, args=(j, k)) for k, j in enumerate(jobs)]
+    [t.start() for t in ts]; [t.join() for t in ts]
+    assert not errors, errors
+
+
 # ---- host-fed pipeline, edge cases, errors ---------------------------------------------------------------
 
 def test_host_pipeline_equals_device_path(torch):
