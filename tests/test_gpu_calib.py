@@ -447,6 +447,27 @@ def test_host_pipeline_equals_device_path(torch):
     kat.assert_same_bits(ref, _oracle_batch(spec, raw, consts))
 
 
+@pytest.mark.parametrize("cm", [None, (7, 4, 50.0, 10), (7, 2, 50.0, 10)])
+def test_host_pipeline_image_modes(torch, cm):
+    """Image output through the chunked host pipeline: the scatter kernel (no common mode), the fused bank-median path and the
+    scratch + gather path, each with its gap fill forked off the pipeline's compute stream, ragged last chunk included."""
+    spec = syn.EPIX10K2M.with_nseg(4)
+    consts = syn.make_constants(spec, seed=74)
+    raw = syn.make_raw_frames(spec, consts, 7, seed=75)
+    iX, iY = syn.make_pixel_index_arrays(spec)
+    cal = _calibrator(spec, consts)
+    cal.set_common_mode(cm)
+    cal.set_geometry(iX, iY)
+    cal.set_host_chunk(3, 2)
+    exp = np.stack([oc.det_image(spec.kind, raw[f], consts, iX, iY, cm) for f in range(7)])
+    h_raw = torch.from_numpy(raw.view(np.int16)).pin_memory()
+    d_out = torch.full(cal.out_shape(7, True), float("nan"), device="cuda")
+    h_out = torch.empty(cal.out_shape(7, True), dtype=torch.float32).pin_memory()
+    cal.calib_host(h_raw, h_out=h_out, d_out=d_out, image=True)
+    kat.assert_same_bits(d_out.cpu().numpy().reshape(exp.shape), exp, "device copy")
+    kat.assert_same_bits(h_out.numpy().reshape(exp.shape), exp, "host copy")
+
+
 def test_empty_batch_and_errors(torch):
     from psana_ray import _native as N
     from psana_ray.calib import GpuCalibrator
