@@ -456,6 +456,153 @@ __device__ __forceinline__ void block_median_keys(const K& key, uint32_t elig, i
     lo_out = lo; hi_out = hi;
 }
 
+// ---- median of the CTA's eligible values on a LINEAR-quantised histogram ---------------------------
+// The values of a bank tile sit within a few ADU of its common-mode offset, so their float keys share the
+// sign/exponent bits and a radix pass on those spends its 2048 bins on a handful of them.  Instead the bin
+// is bin(x) = floor(x * 32) - cs + 1024 (1/32 ADU wide, a 64-ADU window around the centre cs / 32, values
+// outside clamped into the first/last bin) -- monotone in x, so the bin in which the cumulative count
+// crosses rank k holds the k-th smallest value, and with sigma ~ 3 ADU that bin holds a few dozen of the
+// 8 448 values: they are collected and ranked directly by as many threads.  One histogram pass, one
+// collection pass, no float <-> key transform per pixel.  floor(x * 32 + K) comes from one round-down FMA
+// whose result lies in [2^23, 2^24): its low mantissa bits ARE the integer (x * 32 is exact, K is an
+// integer), so the collection test blo <= x < bhi selects exactly the members of the bin.
+// Anything unusual -- rank in a clamp bin, more than CAP values in the bin -- runs the 3-pass radix select
+// on float keys made on the fly: same exact answer.  The centre follows the previous frame's median.
+constexpr int   LQ_NB = 2048;
+constexpr float LQ_SCALE = 32.0f;
+constexpr int   LQ_CS_MAX = 1 << 21;
+
+template <int NK>
+struct FloatKeys {                       // order-preserving integer keys of a register array of floats, made on the fly
+    const float (&x)[NK];
+    __device__ __forceinline__ uint32_t operator[](int i) const { return psr_f2key(x[i]); }
+};
+
+// k-th smallest (0-based) eligible value by a 32-step binary search on the float keys, one block-wide count per bit:
+// small and slow, for the unusual tiles only (block_median_linear's way out).  Not inlined, and fed from a copy of the
+// values in local memory, so that it costs the usual path no registers.  Every thread of the CTA must call it.
+template <int NT, int NK>
+__device__ __noinline__ uint32_t block_kth_bitwise(const float* xs, uint32_t elig, int k, int* redbuf)
+{
+    __syncthreads();                                  // the caller's last reduction is done with redbuf
+    BlockRed<NT / 32> red{redbuf, 0};
+    uint32_t pre = 0;
+#pragma unroll 1
+    for (int bit = 31; bit >= 0; --bit) {
+        const uint32_t cand = pre | (1u << bit);
+        int cnt = 0;
+#pragma unroll 1
+        for (int i = 0; i < NK; ++i) cnt += ((elig & (1u << i)) && psr_f2key(xs[i]) < cand) ? 1 : 0;
+        cnt = red.sum(cnt);
+        if (cnt <= k) pre = cand;
+    }
+    __syncthreads();
+    return pre;
+}
+
+// hist: LQ_NB words, all zero on entry and on exit; sh: 48 ints (16-byte aligned); list: CAP + 4 floats.
+// Returns false (uniformly) when fewer than max(npix_min, 1) values are eligible; else lo/hi = the two middle
+// order statistics.  Every thread of the CTA must call it.
+template <int NT, int NK, int CAP>
+__device__ __forceinline__ bool block_median_linear(const float (&x)[NK], uint32_t elig, int npix_min, int cs,
+                                                    uint32_t* hist, int* sh, float* list, BlockRed<NT / 32>& red,
+                                                    float& lo_out, float& hi_out)
+{
+    constexpr int NSCAN = LQ_NB / 8;                 // threads that scan 8 bins each
+    static_assert(NT >= NSCAN && NSCAN % 32 == 0 && CAP <= NT && CAP % 4 == 0, "scan / rank layout");
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t haddr = (uint32_t)__cvta_generic_to_shared(hist);
+    {
+        const float tlo = (float)(cs - LQ_NB / 2) * (1.0f / LQ_SCALE);            // lower edge of bin 0
+        const float thi = (float)(cs + LQ_NB / 2 - 1) * (1.0f / LQ_SCALE);        // lower edge of the last bin
+        const float kmag = 8388608.0f + (float)(LQ_NB / 2 - cs);                  // 2^23 + NB/2 - cs, an exact integer
+        const uint32_t cadd = haddr - 0x2C000000u;                                // bits(2^23) * 4 mod 2^32
+#pragma unroll
+        for (int i = 0; i < NK; ++i) {
+            const float t = fminf(fmaxf(x[i], tlo), thi);
+            const uint32_t a = __float_as_uint(__fmaf_rd(t, LQ_SCALE, kmag)) * 4u + cadd;
+            asm volatile("{ .reg .pred q; setp.ne.u32 q, %1, 0; @q red.shared.add.u32 [%0], 1; }"
+                         :: "r"(a), "r"(elig & (1u << i)) : "memory");
+        }
+    }
+    __syncthreads();
+    uint32_t b[8]; uint32_t s = 0, incl = 0;
+    if (tid < NSCAN) {
+        uint4* h4 = reinterpret_cast<uint4*>(hist) + 2 * tid;
+        const uint4 u = h4[0], v = h4[1];
+        h4[0] = make_uint4(0, 0, 0, 0); h4[1] = make_uint4(0, 0, 0, 0);           // the owner leaves its bins zero
+        b[0] = u.x; b[1] = u.y; b[2] = u.z; b[3] = u.w; b[4] = v.x; b[5] = v.y; b[6] = v.z; b[7] = v.w;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += b[j];
+        incl = s;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+        if (lane == 31) sh[warp] = (int)incl;
+    }
+    __syncthreads();
+    int n = 0; uint32_t base = 0;
+    {
+        const int4 t0 = reinterpret_cast<const int4*>(sh)[0], t1 = reinterpret_cast<const int4*>(sh)[1];
+        const int tw[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+#pragma unroll
+        for (int w = 0; w < NSCAN / 32; ++w) { n += tw[w]; base += (w < warp) ? (uint32_t)tw[w] : 0u; }
+    }
+    if (n < npix_min || n < 1) return false;                                      // uniform; hist is zero again
+    const int k1 = (n - 1) >> 1, k2 = n >> 1;
+    if (tid < NSCAN) {
+        const uint32_t excl = base + incl - s;
+        if ((uint32_t)k1 >= excl && (uint32_t)k1 < excl + s) {
+            uint32_t r = (uint32_t)k1 - excl; bool done = false;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (!done) { if (r < b[j]) { sh[32] = 8 * tid + j; sh[33] = (int)r; sh[34] = (int)b[j]; done = true; } else r -= b[j]; }
+        }
+    }
+    if (tid == NT - 1) sh[35] = 0;
+    __syncthreads();
+    const int B = sh[32], r = sh[33], M = sh[34];
+    float lo; float hi = 0.f; bool need_hi = k2 != k1;
+    if (B > 0 && B < LQ_NB - 1 && M <= CAP) {                                     // uniform
+        const float blo = (float)(B - LQ_NB / 2 + cs) * (1.0f / LQ_SCALE), bhi = (float)(B - LQ_NB / 2 + cs + 1) * (1.0f / LQ_SCALE);
+#pragma unroll
+        for (int i = 0; i < NK; ++i)
+            if ((elig & (1u << i)) && x[i] >= blo && x[i] < bhi) list[atomicAdd(&sh[35], 1)] = x[i];
+        if (tid < 4) list[M + tid] = __int_as_float(0x7f800000);                  // pad to a multiple of four
+        __syncthreads();
+        if (tid < M) {
+            const float v = list[tid];
+            int lt = 0, le = 0;
+            for (int j = 0; j < M; j += 4) {
+                const float4 u = *reinterpret_cast<const float4*>(list + j);
+                lt += (u.x < v) + (u.y < v) + (u.z < v) + (u.w < v);
+                le += (u.x <= v) + (u.y <= v) + (u.z <= v) + (u.w <= v);
+            }
+            if (lt <= r && r < le) sh[37] = __float_as_int(v);
+            if (lt <= r + 1 && r + 1 < le) sh[38] = __float_as_int(v);
+        }
+        __syncthreads();
+        lo = __int_as_float(sh[37]);
+        if (need_hi && r + 1 < M) { hi = __int_as_float(sh[38]); need_hi = false; }
+    } else {
+        float xs[NK];
+#pragma unroll
+        for (int i = 0; i < NK; ++i) xs[i] = x[i];
+        lo = psr_key2f(block_kth_bitwise<NT, NK>(xs, elig, k1, red.buf));
+    }
+    if (k2 == k1) hi = lo;
+    else if (need_hi) {                                                           // uniform, rare: lo is the last of its bin
+        int cle = 0; uint32_t mg = 0xFFFFFFFFu;
+#pragma unroll
+        for (int i = 0; i < NK; ++i)
+            if (elig & (1u << i)) { cle += (x[i] <= lo); if (x[i] > lo) mg = min(mg, psr_f2key(x[i])); }
+        cle = red.sum(cle);
+        mg = red.minu(mg);
+        hi = cle <= k2 ? psr_key2f(mg) : lo;
+    }
+    lo_out = lo; hi_out = hi;
+    return true;
+}
+
 // smem flag byte of a tile pixel: bit0 mask, bit1 eligible (this frame), bit3 keep, bits 4-5 gain selector
 //   epix10ka selector: data bit 14;  jungfrau selector: 0,1,2 = g0,g1,g2, 3 = none
 template <int DET, int ROWS, int COLS, int NB, int NT>
@@ -890,24 +1037,25 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
 
 // =================================================================================================
 // epix10ka, mode 4, FRAMES-INNER: a CTA owns one bank tile and walks `fpc` frames of the batch.  The
-// tile's pedestals (both bit-14 entries, 67.6 KB) and flag bytes are staged ONCE in shared memory --
-// each thread only ever reads the slots of its own 24 pixels, so no barrier guards them -- which
-// removes most of the per-frame constant traffic from L2 that bounded the one-frame-per-CTA kernel
-// (profiles/README.md: 394 of 702 us).  The gain factors of the epilogue still come from L2.
+// tile's pedestals (both bit-14 entries, 67.6 KB) are staged ONCE in shared memory -- each thread only
+// ever reads the slots of its own 24 pixels, so no barrier guards them -- and the per-pixel flag bits
+// (mask, keep, eligibility for either bit-14 state) sit in four registers as 24-bit planes, so that a
+// frame's eligibility is one logic operation on the plane of its bit-14 states.  The values stay in
+// registers as floats from load to store; the median comes from block_median_linear.  The gain factors
+// of the epilogue come from L2.
 // =================================================================================================
 template <int NT, int MINB, bool IMG>
 __global__ void __launch_bounds__(NT, MINB)
 cm_banks_epix_fi_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c, int nframes, int fpc)
 {
     constexpr int ROWS = 352, COLS = 384, NB = 8, TR = ROWS / 2, TC = COLS / NB, CH = TC / 8, NCH = TR * CH, CPT = NCH / NT, NK = CPT * 8;
-    constexpr int NW = NT / 32;
+    constexpr int NW = NT / 32, CAP = NT / 4 * 4;
     static_assert(NCH % NT == 0 && NT % 32 == 0 && NK <= 32, "tile must split evenly over the CTA");
     extern __shared__ float4 sm4[];                               // [4][NCH]: ped0 px0-3, ped0 px4-7, ped1 px0-3, ped1 px4-7
-    uint2* sfl = reinterpret_cast<uint2*>(sm4 + 4 * NCH);         // [NCH] flag bytes of the chunk
     __shared__ int redbuf[64];
-    __shared__ uint32_t hist[2048];
-    __shared__ uint32_t list[LISTCAP + 32];
-    __shared__ int selsh[40];
+    __shared__ __align__(16) uint32_t hist[LQ_NB];
+    __shared__ __align__(16) float list[CAP + 4];
+    __shared__ __align__(16) int selsh[48];
 
     const int tid = threadIdx.x;
     int bid = blockIdx.x;
@@ -915,9 +1063,10 @@ cm_banks_epix_fi_kernel(const uint16_t* __restrict__ raw, float* __restrict__ ou
     const int half = bid & 1;  bid >>= 1;
     const int seg = bid;
     const int f_begin = blockIdx.y * fpc, f_end = min(nframes, f_begin + fpc);
-    const uint32_t keep_or = c.ignore_keep ? 0x08080808u : 0u;
 
+    for (int i = tid; i < LQ_NB; i += NT) hist[i] = 0u;
     int gpj[CPT];
+    uint32_t mbits = 0, kbits = 0, e0bits = 0, e1bits = 0;        // bit q = pixel q of this thread
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
         const int ch = tid + j * NT;
@@ -928,10 +1077,18 @@ cm_banks_epix_fi_kernel(const uint16_t* __restrict__ raw, float* __restrict__ ou
         sm4[1 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped0 + gp) + 1);
         sm4[2 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped1 + gp));
         sm4[3 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped1 + gp) + 1);
-        uint2 f = __ldg(reinterpret_cast<const uint2*>(c.flags + gp));
-        f.x |= keep_or; f.y |= keep_or;
-        sfl[ch] = f;
+        const uint2 f = __ldg(reinterpret_cast<const uint2*>(c.flags + gp));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t fb = ((i < 4 ? f.x : f.y) >> (8 * (i & 3))) & 0xFFu;
+            const int q = j * 8 + i;
+            mbits |= ((fb & PSR_FL_MASK) ? 1u : 0u) << q;
+            kbits |= ((fb & PSR_FL_KEEP) ? 1u : 0u) << q;
+            e0bits |= ((fb & PSR_FL_ELIG0) ? 1u : 0u) << q;
+            e1bits |= ((fb & PSR_FL_ELIG1) ? 1u : 0u) << q;
+        }
     }
+    if (c.ignore_keep) kbits = 0xFFFFFFFFu;
     // IMG: where each chunk goes in the assembled image is the same for every frame
     int t0j[IMG ? CPT : 1]; uint32_t kinds = 0;
     if constexpr (IMG) {
@@ -939,13 +1096,15 @@ cm_banks_epix_fi_kernel(const uint16_t* __restrict__ raw, float* __restrict__ ou
         for (int j = 0; j < CPT; ++j) kinds |= img_chunk_kind<8>(c.fwd + gpj[j], t0j[j]) << (2 * j);
     }
     const size_t fout = IMG ? (size_t)c.H * c.W : (size_t)c.npix;
+    __syncthreads();
 
     BlockRed<NW> red{redbuf, 0};
+    int cs = 0;                                                   // histogram centre * 32: the previous frame's median
     for (int frame = f_begin; frame < f_end; ++frame) {
         const uint16_t* rawf = raw + (size_t)frame * c.npix;
         float* outf = out + (size_t)frame * fout;
-        uint32_t key[NK];
-        uint32_t elig = 0, sel0 = 0;
+        float x[NK];
+        uint32_t sbits = 0;                                       // bit q = data bit 14 of pixel q
 #pragma unroll
         for (int j = 0; j < CPT; ++j) {
             const int ch = tid + j * NT;
@@ -954,54 +1113,48 @@ cm_banks_epix_fi_kernel(const uint16_t* __restrict__ raw, float* __restrict__ ou
             const float4 a0 = sm4[0 * NCH + ch], a1 = sm4[1 * NCH + ch], b0 = sm4[2 * NCH + ch], b1 = sm4[3 * NCH + ch];
             const float pa[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
             const float pb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-            const uint2 fv = sfl[ch];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int q = j * 8 + i;
-                const uint32_t v = (i & 1) ? (w[i >> 1] >> 16) : (w[i >> 1] & 0xFFFFu);
-                const uint32_t f = (i < 4 ? fv.x : fv.y) >> (8 * (i & 3));
-                const uint32_t sel = (v >> 14) & 1u;
-                const float x = __fsub_rn((float)(v & 0x3FFFu), sel ? pb[i] : pa[i]);
-                const uint32_t el = sel ? (f & PSR_FL_ELIG1) : (f & PSR_FL_ELIG0);
-                key[q] = psr_f2key(x);
-                elig |= (el ? 1u : 0u) << q;
-                sel0 |= sel << q;
+                const uint32_t v = (i & 1) ? (w[i >> 1] >> 16) : w[i >> 1];
+                const bool sel = (v & 0x4000u) != 0;
+                x[q] = __fsub_rn((float)(v & 0x3FFFu), sel ? pb[i] : pa[i]);
+                if (sel) sbits |= 1u << q;
             }
         }
+        const uint32_t elig = (sbits & e1bits) | (~sbits & e0bits);
 
         // common_mode_2d: skip if n < npix_min, skip if |cm| > cormax
-        const int n = red.sum(__popc(elig));
-        float cm = 0.f; bool apply = false;
-        if (n >= c.npix_min && n > 0) {                        // uniform across the CTA
-            uint32_t lo, hi;
-            block_median_keys<NT, NK, NW>(key, elig, n, hist, selsh, list, red, lo, hi);
-            cm = psr_mid(psr_key2f(lo), psr_key2f(hi));
-            apply = !(fabsf(cm) > c.cormax);
+        float lo, hi, cm = 0.f;
+        if (block_median_linear<NT, NK, CAP>(x, elig, c.npix_min, cs, hist, selsh, list, red, lo, hi)) {      // uniform
+            const float med = psr_mid(lo, hi);
+            if (!(fabsf(med) > c.cormax)) cm = med;
+            const float t = fminf(fmaxf(__fmul_rn(med, LQ_SCALE), -(float)LQ_CS_MAX), (float)LQ_CS_MAX);
+            cs = __float2int_rn(t);
         }
+        // an unapplied correction is cm = +0: x - 0 == x exactly, for every x
 
 #pragma unroll
         for (int j = 0; j < CPT; ++j) {
-            const int ch = tid + j * NT;
             const int gp = gpj[j];
-            float ga[8], gb_[8];
-            ld8(c.gf0 + gp, ga); ld8(c.gf1 + gp, gb_);
-            const uint2 fv = sfl[ch];
             float o[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int q = j * 8 + i;
-                const uint32_t f = (i < 4 ? fv.x : fv.y) >> (8 * (i & 3));
-                float x = psr_key2f(key[q]);
-                if (apply && ((elig >> q) & 1u)) x = __fsub_rn(x, cm);
-                const float gf = ((sel0 >> q) & 1u) ? gb_[i] : ga[i];
-                const float v = __fmul_rn(__fmul_rn(x, gf), (f & PSR_FL_MASK) ? 1.0f : 0.0f);
-                o[i] = (f & PSR_FL_KEEP) ? v : 0.0f;
+            for (int h = 0; h < 2; ++h) {
+                const float4 ga = __ldg(reinterpret_cast<const float4*>(c.gf0 + gp) + h), gb = __ldg(reinterpret_cast<const float4*>(c.gf1 + gp) + h);
+                const float g0[4] = {ga.x, ga.y, ga.z, ga.w}, g1[4] = {gb.x, gb.y, gb.z, gb.w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int q = j * 8 + h * 4 + i;
+                    float xv = x[q];
+                    if (elig & (1u << q)) xv = __fsub_rn(xv, cm);
+                    const float gf = (sbits & (1u << q)) ? g1[i] : g0[i];
+                    float v = __fmul_rn(xv, gf);
+                    v = __fmul_rn(v, (mbits & (1u << q)) ? 1.0f : 0.0f);
+                    o[h * 4 + i] = (kbits & (1u << q)) ? v : 0.0f;
+                }
+                if constexpr (!IMG) __stcs(reinterpret_cast<float4*>(outf + gp) + h, make_float4(o[h * 4], o[h * 4 + 1], o[h * 4 + 2], o[h * 4 + 3]));
             }
             if constexpr (IMG) img_store_chunk<8>(outf, c.fwd + gp, (kinds >> (2 * j)) & 3u, t0j[j], o);
-            else {
-                __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
-                __stcs(reinterpret_cast<float4*>(outf + gp + 4), make_float4(o[4], o[5], o[6], o[7]));
-            }
         }
     }
 }
@@ -1021,7 +1174,7 @@ constexpr int EPIX_NT = 352, JF_NT = 512;
 #endif
 constexpr size_t EPIX_SMEM = ((size_t)(176 * 49) * 5 + 15) / 16 * 16 + (EPIX_NT / 32) * 4 * 256 * 4;   // padded tile (float + flag byte) + warp histograms
 constexpr size_t JF_SMEM = ((size_t)(256 * 65) * 5 + 15) / 16 * 16 + (JF_NT / 32) * 4 * 256 * 4;
-constexpr size_t EPIX_FI_SMEM = (size_t)1056 * (4 * 16 + 8);     // pedestals + flag bytes of one bank tile
+constexpr size_t EPIX_FI_SMEM = (size_t)1056 * (4 * 16);         // pedestals of one bank tile
 #ifndef PSR_CM_FPC
 #define PSR_CM_FPC 8           /* frames per CTA of the frames-inner common-mode kernel */
 #endif
