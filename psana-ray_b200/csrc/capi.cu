@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <cmath>
 #include <algorithm>
 #include <mutex>
 #include <new>
@@ -113,7 +114,17 @@ int rebuild_flags(psr_ctx* c) {
         fl[i] = (uint8_t)f;
     }
     PSR_CUDA(cudaMemcpy(c->d_flags, fl.data(), (size_t)n, cudaMemcpyHostToDevice));
+    c->dev.has_keep = c->h_keep_calib.empty() ? 0 : 1;
     return PSR_OK;
+}
+
+// The mask is folded into the gain factors: a masked pixel's factor becomes factor * 0 = +-0, so that x * factor is already
+// the (x * factor) * 0 psana computes (same sign of zero, NaN stays NaN) and kernels may skip the mask multiply; kernels that
+// still multiply get the same bits.  The two differ only if x * factor overflows float32 on a masked pixel (inf * 0 = NaN
+// there, +-0 here): such constants are refused instead of silently calibrated differently.
+inline bool fold_overflows(float gf, float ped, float off) {
+    if (!std::isfinite(gf) || !std::isfinite(ped) || !std::isfinite(off)) return false;     // non-finite inputs give NaN either way
+    return (double)std::fabs(gf) * (16383.0 + std::fabs((double)ped) + std::fabs((double)off)) >= 1.0e38;
 }
 
 // device copy of the forward map with the image keep mask folded in (~index = "store 0 there")
@@ -318,6 +329,11 @@ int psr_set_constants(psr_ctx* c, const float* h_peds, const float* h_gain, cons
                 g0[i] = m0 < 7 ? gfac_of(h_gain[(size_t)m0 * n + i]) : 1.0f;
                 p1[i] = m1 < 7 ? h_peds[(size_t)m1 * n + i] : 0.0f;
                 g1[i] = m1 < 7 ? gfac_of(h_gain[(size_t)m1 * n + i]) : 1.0f;
+                if (h_mask && !h_mask[i]) {
+                    if (fold_overflows(g0[i], p0[i], 0.f) || fold_overflows(g1[i], p1[i], 0.f))
+                        return fail(PSR_E_UNSUPPORTED, "masked pixel %zu: 1/gain times the pixel's value range overflows float32", i);
+                    g0[i] = g0[i] * 0.0f; g1[i] = g1[i] * 0.0f;
+                }
             }
             c->consts_bytes = 4 * n * sizeof(float) + n;
             PSR_CUDA(cudaMalloc(&c->d_consts, c->consts_bytes));
@@ -332,6 +348,11 @@ int psr_set_constants(psr_ctx* c, const float* h_peds, const float* h_gain, cons
             const size_t m = 3 * n;
             std::vector<float> gf(m);
             for (size_t i = 0; i < m; ++i) gf[i] = h_gain ? gfac_of(h_gain[i]) : 1.0f;
+            if (h_mask) for (size_t i = 0; i < m; ++i) if (!h_mask[i % n]) {
+                if (fold_overflows(gf[i], h_peds[i], h_offs ? h_offs[i] : 0.f))
+                    return fail(PSR_E_UNSUPPORTED, "masked pixel %zu: 1/gain times the pixel's value range overflows float32", i % n);
+                gf[i] = gf[i] * 0.0f;
+            }
             c->consts_bytes = (h_offs ? 3 : 2) * m * sizeof(float);
             PSR_CUDA(cudaMalloc(&c->d_consts, c->consts_bytes));
             float* d = static_cast<float*>(c->d_consts);

@@ -35,6 +35,18 @@
 #ifndef PSR_CMB_JF_MINB
 #define PSR_CMB_JF_MINB (PSR_CMB_JF_KS ? 2 : 1)
 #endif
+#ifndef PSR_CMF_MAGIC           /* frames-inner kernel: int -> float through 2^23 + v (FMA pipe) instead of a conversion */
+#define PSR_CMF_MAGIC 1
+#endif
+#ifndef PSR_CMF_CHAIN           /* frames-inner kernel: chunk j + 1's loads wait for chunk j's values (bounds registers) */
+#define PSR_CMF_CHAIN 1
+#endif
+#ifndef PSR_CMF_SELASM          /* selects as predicated second operations (FMA pipe) */
+#define PSR_CMF_SELASM 1
+#endif
+#ifndef PSR_LQ_ATOM             /* histogram update: 1 = unconditional add of 0/1, 0 = increment under a branch */
+#define PSR_LQ_ATOM 1
+#endif
 #ifndef PSR_CM_MATCH
 #define PSR_CM_MATCH 0
 #endif
@@ -456,84 +468,91 @@ __device__ __forceinline__ void block_median_keys(const K& key, uint32_t elig, i
     lo_out = lo; hi_out = hi;
 }
 
-// ---- median of the CTA's eligible values on a LINEAR-quantised histogram ---------------------------
-// The values of a bank tile sit within a few ADU of its common-mode offset, so their float keys share the
-// sign/exponent bits and a radix pass on those spends its 2048 bins on a handful of them.  Instead the bin
-// is bin(x) = floor(x * 32) - cs + 1024 (1/32 ADU wide, a 64-ADU window around the centre cs / 32, values
-// outside clamped into the first/last bin) -- monotone in x, so the bin in which the cumulative count
-// crosses rank k holds the k-th smallest value, and with sigma ~ 3 ADU that bin holds a few dozen of the
-// 8 448 values: they are collected and ranked directly by as many threads.  One histogram pass, one
-// collection pass, no float <-> key transform per pixel.  floor(x * 32 + K) comes from one round-down FMA
-// whose result lies in [2^23, 2^24): its low mantissa bits ARE the integer (x * 32 is exact, K is an
-// integer), so the collection test blo <= x < bhi selects exactly the members of the bin.
-// Anything unusual -- rank in a clamp bin, more than CAP values in the bin -- runs the 3-pass radix select
-// on float keys made on the fly: same exact answer.  The centre follows the previous frame's median.
-constexpr int   LQ_NB = 2048;
-constexpr float LQ_SCALE = 32.0f;
-constexpr int   LQ_CS_MAX = 1 << 21;
-
-template <int NK>
-struct FloatKeys {                       // order-preserving integer keys of a register array of floats, made on the fly
-    const float (&x)[NK];
-    __device__ __forceinline__ uint32_t operator[](int i) const { return psr_f2key(x[i]); }
-};
-
-// k-th smallest (0-based) eligible value by a 32-step binary search on the float keys, one block-wide count per bit:
-// small and slow, for the unusual tiles only (block_median_linear's way out).  Not inlined, and fed from a copy of the
-// values in local memory, so that it costs the usual path no registers.  Every thread of the CTA must call it.
-template <int NT, int NK>
-__device__ __noinline__ uint32_t block_kth_bitwise(const float* xs, uint32_t elig, int k, int* redbuf)
-{
-    __syncthreads();                                  // the caller's last reduction is done with redbuf
-    BlockRed<NT / 32> red{redbuf, 0};
-    uint32_t pre = 0;
-#pragma unroll 1
-    for (int bit = 31; bit >= 0; --bit) {
-        const uint32_t cand = pre | (1u << bit);
-        int cnt = 0;
-#pragma unroll 1
-        for (int i = 0; i < NK; ++i) cnt += ((elig & (1u << i)) && psr_f2key(xs[i]) < cand) ? 1 : 0;
-        cnt = red.sum(cnt);
-        if (cnt <= k) pre = cand;
-    }
-    __syncthreads();
-    return pre;
+// Selects written as a predicated second operation: the arithmetic runs on the FMA pipe, which has room, instead
+// of a select on the ALU pipe, which is the one these kernels fill.  Same roundings as select-then-operate.
+__device__ __forceinline__ float psr_sub_sel(float f, float pa, float pb, uint32_t pick_b) {        // f - (pick_b ? pb : pa)
+#if !PSR_CMF_SELASM
+    return __fsub_rn(f, pick_b ? pb : pa);
+#endif
+    float r;
+    asm("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %4, 0;\n\tsub.rn.f32 %0, %1, %2;\n\t@p sub.rn.f32 %0, %1, %3;\n\t}" : "=&f"(r) : "f"(f), "f"(pa), "f"(pb), "r"(pick_b));
+    return r;
+}
+__device__ __forceinline__ float psr_mul_sel(float f, float ga, float gb, uint32_t pick_b) {        // f * (pick_b ? gb : ga)
+#if !PSR_CMF_SELASM
+    return __fmul_rn(f, pick_b ? gb : ga);
+#endif
+    float r;
+    asm("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %4, 0;\n\tmul.rn.f32 %0, %1, %2;\n\t@p mul.rn.f32 %0, %1, %3;\n\t}" : "=&f"(r) : "f"(f), "f"(ga), "f"(gb), "r"(pick_b));
+    return r;
+}
+__device__ __forceinline__ float psr_sub_if(float f, float d, uint32_t on) {                        // on ? f - d : f
+#if !PSR_CMF_SELASM
+    return on ? __fsub_rn(f, d) : f;
+#endif
+    asm("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p sub.rn.f32 %0, %0, %1;\n\t}" : "+f"(f) : "f"(d), "r"(on));
+    return f;
 }
 
-// hist: LQ_NB words, all zero on entry and on exit; sh: 48 ints (16-byte aligned); list: CAP + 4 floats.
-// Returns false (uniformly) when fewer than max(npix_min, 1) values are eligible; else lo/hi = the two middle
-// order statistics.  Every thread of the CTA must call it.
-template <int NT, int NK, int CAP>
-__device__ __forceinline__ bool block_median_linear(const float (&x)[NK], uint32_t elig, int npix_min, int cs,
-                                                    uint32_t* hist, int* sh, float* list, BlockRed<NT / 32>& red,
-                                                    float& lo_out, float& hi_out)
+// ---- median of the CTA's eligible values on a LINEAR-quantised histogram ---------------------------
+// The values of a bank tile sit within a few ADU of its common-mode offset, so their float keys share the
+// sign/exponent bits and a radix pass on those spends its 2048 bins on a handful of them.  Instead:
+//     y = sat(x * a + b)  in [0, 1]   (one saturating FMA: a = 1/64 per ADU, b = 0.5 - centre * a)
+//     bin(x) = floor(y * 2047)        (one round-down FMA onto 2^23: the low mantissa bits are the integer)
+// -- about 1/32 ADU per bin in a 64-ADU window around the centre, everything outside in bins 0 / 2047.
+// bin() is monotone in x (a composition of monotone roundings), so the bin in which the cumulative count
+// crosses rank k holds the k-th smallest value, and with sigma ~ 3 ADU that bin holds a few dozen of the
+// tile's values: they are collected (the same two FMAs decide membership, so the set is exactly the bin's)
+// and ranked directly by as many threads.  One histogram pass, one collection pass, no float <-> key
+// transform, and the arithmetic is on the FMA pipe rather than the ALU pipe the rest of the kernel loads.
+// The centre follows the previous frame's median.  If the rank lands in an end bin the window is relocated:
+// one pass at 32 ADU per bin over +-32768 ADU, then the fine pass again around the bin that pass found.
+// Whatever is still unusual (values beyond that, more than CAP values in one bin) takes the bitwise
+// search -- same exact answer.
+constexpr int   LQ_NB = 2048;
+constexpr float LQ_A = 1.0f / 64.0f;          // fine window: 64 ADU
+constexpr float LQ_A_COARSE = 1.0f / 65536.0f;
+
+// bits of 2^23 + bin(x): the histogram address is bits * 4 + (base - bits(2^23) * 4), all in 32-bit wrap-around
+__device__ __forceinline__ uint32_t lq_bits(float x, float a, float b) {
+    return __float_as_uint(__fmaf_rd(__saturatef(__fmaf_rn(x, a, b)), (float)(LQ_NB - 1), 8388608.0f));
+}
+
+struct BitsLinear { static __device__ __forceinline__ constexpr int pos(int i) { return i; } };
+// value i = pixel (2k + h) of chunk j (i = 8j + 2k + h: word k of the chunk's four raw words, low / high half):
+// bit 4j + k + 16h, the place where ONE shift of the raw word drops its two bit-14 flags
+struct BitsEpixWords { static __device__ __forceinline__ constexpr int pos(int i) { return 4 * (i >> 3) + ((i & 7) >> 1) + 16 * (i & 1); } };
+
+struct LocalVals { const float* p; __device__ __forceinline__ float operator[](int i) const { return p[i]; } };
+
+// One histogram pass + scan: on return sh[32] = bin holding rank k1 = (n - 1) / 2, sh[33] = rank inside it, sh[34] = its
+// population, sh[36] = n (eligible values), sh[35] = 0; hist is zero again.  Every thread of the CTA must call it.
+template <int NT, int NK, typename BP, typename X>
+__device__ __forceinline__ void lq_pass(const X& x, uint32_t elig, float a, float b, uint32_t* hist, int* sh)
 {
     constexpr int NSCAN = LQ_NB / 8;                 // threads that scan 8 bins each
-    static_assert(NT >= NSCAN && NSCAN % 32 == 0 && CAP <= NT && CAP % 4 == 0, "scan / rank layout");
+    static_assert(NT >= NSCAN && NSCAN % 32 == 0, "scan layout");
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t haddr = (uint32_t)__cvta_generic_to_shared(hist);
-    {
-        const float tlo = (float)(cs - LQ_NB / 2) * (1.0f / LQ_SCALE);            // lower edge of bin 0
-        const float thi = (float)(cs + LQ_NB / 2 - 1) * (1.0f / LQ_SCALE);        // lower edge of the last bin
-        const float kmag = 8388608.0f + (float)(LQ_NB / 2 - cs);                  // 2^23 + NB/2 - cs, an exact integer
-        const uint32_t cadd = haddr - 0x2C000000u;                                // bits(2^23) * 4 mod 2^32
+    const uint32_t cadd = (uint32_t)__cvta_generic_to_shared(hist) - 0x2C000000u;        // bits(2^23) * 4 mod 2^32
 #pragma unroll
-        for (int i = 0; i < NK; ++i) {
-            const float t = fminf(fmaxf(x[i], tlo), thi);
-            const uint32_t a = __float_as_uint(__fmaf_rd(t, LQ_SCALE, kmag)) * 4u + cadd;
-            asm volatile("{ .reg .pred q; setp.ne.u32 q, %1, 0; @q red.shared.add.u32 [%0], 1; }"
-                         :: "r"(a), "r"(elig & (1u << i)) : "memory");
-        }
+    for (int i = 0; i < NK; ++i) {
+        const uint32_t ad = lq_bits(x[i], a, b) * 4u + cadd;
+#if PSR_LQ_ATOM
+        const uint32_t m = (elig << (31 - BP::pos(i))) >> 31;                             // ineligible: add 0 (no branch around the atomic)
+        asm volatile("red.shared.add.u32 [%0], %1;" :: "r"(ad), "r"(m) : "memory");
+#else
+        asm volatile("{ .reg .pred q; setp.ne.u32 q, %1, 0; @q red.shared.add.u32 [%0], 1; }" :: "r"(ad), "r"(elig & (1u << BP::pos(i))) : "memory");
+#endif
     }
     __syncthreads();
-    uint32_t b[8]; uint32_t s = 0, incl = 0;
+    uint32_t bn[8]; uint32_t s = 0, incl = 0;
     if (tid < NSCAN) {
         uint4* h4 = reinterpret_cast<uint4*>(hist) + 2 * tid;
         const uint4 u = h4[0], v = h4[1];
-        h4[0] = make_uint4(0, 0, 0, 0); h4[1] = make_uint4(0, 0, 0, 0);           // the owner leaves its bins zero
-        b[0] = u.x; b[1] = u.y; b[2] = u.z; b[3] = u.w; b[4] = v.x; b[5] = v.y; b[6] = v.z; b[7] = v.w;
+        h4[0] = make_uint4(0, 0, 0, 0); h4[1] = make_uint4(0, 0, 0, 0);                   // the owner leaves its bins zero
+        bn[0] = u.x; bn[1] = u.y; bn[2] = u.z; bn[3] = u.w; bn[4] = v.x; bn[5] = v.y; bn[6] = v.z; bn[7] = v.w;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) s += b[j];
+        for (int j = 0; j < 8; ++j) s += bn[j];
         incl = s;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
@@ -547,59 +566,160 @@ __device__ __forceinline__ bool block_median_linear(const float (&x)[NK], uint32
 #pragma unroll
         for (int w = 0; w < NSCAN / 32; ++w) { n += tw[w]; base += (w < warp) ? (uint32_t)tw[w] : 0u; }
     }
-    if (n < npix_min || n < 1) return false;                                      // uniform; hist is zero again
-    const int k1 = (n - 1) >> 1, k2 = n >> 1;
-    if (tid < NSCAN) {
+    const int k1 = (n - 1) >> 1;
+    if (tid < NSCAN && n > 0) {
         const uint32_t excl = base + incl - s;
         if ((uint32_t)k1 >= excl && (uint32_t)k1 < excl + s) {
-            uint32_t r = (uint32_t)k1 - excl; bool done = false;
+            uint32_t rr = (uint32_t)k1 - excl; bool done = false;
 #pragma unroll
             for (int j = 0; j < 8; ++j)
-                if (!done) { if (r < b[j]) { sh[32] = 8 * tid + j; sh[33] = (int)r; sh[34] = (int)b[j]; done = true; } else r -= b[j]; }
+                if (!done) { if (rr < bn[j]) { sh[32] = 8 * tid + j; sh[33] = (int)rr; sh[34] = (int)bn[j]; done = true; } else rr -= bn[j]; }
         }
     }
-    if (tid == NT - 1) sh[35] = 0;
+    if (tid == NT - 1) { sh[35] = 0; sh[36] = n; }
     __syncthreads();
-    const int B = sh[32], r = sh[33], M = sh[34];
-    float lo; float hi = 0.f; bool need_hi = k2 != k1;
-    if (B > 0 && B < LQ_NB - 1 && M <= CAP) {                                     // uniform
-        const float blo = (float)(B - LQ_NB / 2 + cs) * (1.0f / LQ_SCALE), bhi = (float)(B - LQ_NB / 2 + cs + 1) * (1.0f / LQ_SCALE);
+}
+
+// The members of bin B (fine window b) are collected and ranked by one thread each: lo = rank r, hi = rank r + 1 when
+// the bin holds it (have_hi).  sh[35] must be 0 on entry (lq_pass leaves it so); M <= CAP.  Every thread must call it.
+template <int NT, int NK, int CAP, typename BP, typename X>
+__device__ __forceinline__ void lq_collect_rank(const X& x, uint32_t elig, float b, int B, int r, int M, int* sh, float* list,
+                                                float& lo, float& hi, bool& have_hi)
+{
+    static_assert(CAP <= NT && CAP % 4 == 0, "rank layout");
+    const int tid = threadIdx.x;
+    const uint32_t target = 0x4B000000u + (uint32_t)B;
+    uint32_t hits = 0; float cand = 0.f;
+    asm volatile("" : "+f"(b));                          // the bins are recomputed, not kept from the histogram pass (NK registers)
 #pragma unroll
-        for (int i = 0; i < NK; ++i)
-            if ((elig & (1u << i)) && x[i] >= blo && x[i] < bhi) list[atomicAdd(&sh[35], 1)] = x[i];
-        if (tid < 4) list[M + tid] = __int_as_float(0x7f800000);                  // pad to a multiple of four
-        __syncthreads();
-        if (tid < M) {
-            const float v = list[tid];
-            int lt = 0, le = 0;
-            for (int j = 0; j < M; j += 4) {
-                const float4 u = *reinterpret_cast<const float4*>(list + j);
-                lt += (u.x < v) + (u.y < v) + (u.z < v) + (u.w < v);
-                le += (u.x <= v) + (u.y <= v) + (u.z <= v) + (u.w <= v);
-            }
-            if (lt <= r && r < le) sh[37] = __float_as_int(v);
-            if (lt <= r + 1 && r + 1 < le) sh[38] = __float_as_int(v);
-        }
-        __syncthreads();
-        lo = __int_as_float(sh[37]);
-        if (need_hi && r + 1 < M) { hi = __int_as_float(sh[38]); need_hi = false; }
-    } else {
-        float xs[NK];
-#pragma unroll
-        for (int i = 0; i < NK; ++i) xs[i] = x[i];
-        lo = psr_key2f(block_kth_bitwise<NT, NK>(xs, elig, k1, red.buf));
+    for (int i = 0; i < NK; ++i) {
+        const float xi = x[i];
+        if (lq_bits(xi, LQ_A, b) == target) { hits |= 1u << BP::pos(i); cand = xi; }
     }
-    if (k2 == k1) hi = lo;
-    else if (need_hi) {                                                           // uniform, rare: lo is the last of its bin
-        int cle = 0; uint32_t mg = 0xFFFFFFFFu;
+    // a thread almost never holds two members of the bin: one candidate register, one branch per thread
+    if (hits != 0u) {
+        if ((hits & (hits - 1u)) == 0u) { if (hits & elig) list[atomicAdd(&sh[35], 1)] = cand; }
+        else {
+            hits &= elig;
 #pragma unroll
+            for (int i = 0; i < NK; ++i) if (hits & (1u << BP::pos(i))) list[atomicAdd(&sh[35], 1)] = x[i];
+        }
+    }
+    if (tid < 4) list[M + tid] = __int_as_float(0x7f800000);                              // pad to a multiple of four
+    __syncthreads();
+    if (tid < M) {
+        const float v = list[tid];
+        int lt = 0, le = 0;
+        for (int j = 0; j < M; j += 4) {
+            const float4 u = *reinterpret_cast<const float4*>(list + j);
+            lt += (u.x < v) + (u.y < v) + (u.z < v) + (u.w < v);
+            le += (u.x <= v) + (u.y <= v) + (u.z <= v) + (u.w <= v);
+        }
+        if (lt <= r && r < le) sh[37] = __float_as_int(v);
+        if (lt <= r + 1 && r + 1 < le) sh[38] = __float_as_int(v);
+    }
+    __syncthreads();
+    lo = __int_as_float(sh[37]);
+    have_hi = r + 1 < M;
+    hi = have_hi ? __int_as_float(sh[38]) : lo;
+}
+
+// Everything unusual about a tile's median, in one place and not inlined, so that it costs the usual path neither
+// registers nor code: works on a copy of the values in local memory.
+//   have_lo: the fine pass found lo but the bin does not hold the next value (lo is the last of its bin).
+//   else: the rank fell into an end bin of the fine window, or its bin holds more than CAP values.  End bin: one pass at
+//   32 ADU per bin over +-32768 ADU, the fine window moved to the middle of the bin that pass finds, fine pass + ranking
+//   again.  What even that does not settle goes to a 32-step binary search on the float keys, one block-wide count per bit.
+// out[0] = lo, out[1] = hi, out[2] = the fine window's b as used (unchanged unless relocated).
+template <int NT, int NK, int CAP, typename BP>
+__device__ __noinline__ void lq_median_slow(const float* xs, uint32_t elig, int n, bool have_lo, float lo, float b,
+                                            uint32_t* hist, int* sh, float* list, int* redbuf, float* out)
+{
+    const LocalVals x{xs};
+    const int k1 = (n - 1) >> 1, k2 = n >> 1;
+    float hi = lo; bool have_hi = false;
+    __syncthreads();
+    if (!have_lo) {
+        int B = sh[32];
+        __syncthreads();
+        if (B <= 0 || B >= LQ_NB - 1) {
+            lq_pass<NT, NK, BP>(x, elig, LQ_A_COARSE, 0.5f, hist, sh);
+            B = sh[32];
+            __syncthreads();
+            if (B > 0 && B < LQ_NB - 1) {
+                const float xc = __fmul_rn(__fsub_rn(__fmul_rn((float)B + 0.5f, 1.0f / (float)(LQ_NB - 1)), 0.5f), 1.0f / LQ_A_COARSE);
+                b = __fsub_rn(0.5f, __fmul_rn(xc, LQ_A));
+                lq_pass<NT, NK, BP>(x, elig, LQ_A, b, hist, sh);
+                B = sh[32];
+                const int r = sh[33], M = sh[34];
+                if (B > 0 && B < LQ_NB - 1 && M <= CAP) {
+                    lq_collect_rank<NT, NK, CAP, BP>(x, elig, b, B, r, M, sh, list, lo, hi, have_hi);
+                    have_lo = true;
+                }
+            }
+        }
+        if (!have_lo) {
+            BlockRed<NT / 32> red{redbuf, 0};
+            uint32_t pre = 0;
+#pragma unroll 1
+            for (int bit = 31; bit >= 0; --bit) {
+                const uint32_t cand = pre | (1u << bit);
+                int cnt = 0;
+#pragma unroll 1
+                for (int i = 0; i < NK; ++i) cnt += ((elig & (1u << BP::pos(i))) && psr_f2key(xs[i]) < cand) ? 1 : 0;
+                cnt = red.sum(cnt);
+                if (cnt <= k1) pre = cand;
+            }
+            __syncthreads();
+            lo = psr_key2f(pre); hi = lo;
+        }
+    }
+    if (k2 != k1 && !have_hi) {
+        // the upper middle value: the smallest eligible value above lo, or lo itself when its duplicates reach rank k2
+        BlockRed<NT / 32> red{redbuf, 0};
+        int cle = 0; uint32_t mg = 0xFFFFFFFFu;
+#pragma unroll 1
         for (int i = 0; i < NK; ++i)
-            if (elig & (1u << i)) { cle += (x[i] <= lo); if (x[i] > lo) mg = min(mg, psr_f2key(x[i])); }
+            if (elig & (1u << BP::pos(i))) { cle += (xs[i] <= lo); if (xs[i] > lo) mg = min(mg, psr_f2key(xs[i])); }
         cle = red.sum(cle);
         mg = red.minu(mg);
+        __syncthreads();
         hi = cle <= k2 ? psr_key2f(mg) : lo;
     }
+    if (k2 == k1) hi = lo;
+    out[0] = lo; out[1] = hi; out[2] = b;
+}
+
+// hist: LQ_NB words, all zero on entry and on exit; sh: 48 ints (16-byte aligned); list: CAP + 4 floats;
+// bcen: the window's b = 0.5 - centre / 64, updated to the median found.  Returns false (uniformly) when fewer than
+// max(npix_min, 1) values are eligible; else lo/hi = the two middle order statistics.  Every thread of the CTA must call it.
+template <int NT, int NK, int CAP, typename BP>
+__device__ __forceinline__ bool block_median_linear(const float (&x)[NK], uint32_t elig, int npix_min, float& bcen,
+                                                    uint32_t* hist, int* sh, float* list, int* redbuf,
+                                                    float& lo_out, float& hi_out)
+{
+    float b = bcen;
+    lq_pass<NT, NK, BP>(x, elig, LQ_A, b, hist, sh);
+    const int n = sh[36];
+    if (n < npix_min || n < 1) return false;                                              // uniform
+    const int B = sh[32], r = sh[33], M = sh[34];
+    float lo = 0.f, hi = 0.f; bool have_lo = false, have_hi = false;
+    if (B > 0 && B < LQ_NB - 1 && M <= CAP) {                                             // uniform, the usual case
+        lq_collect_rank<NT, NK, CAP, BP>(x, elig, b, B, r, M, sh, list, lo, hi, have_hi);
+        have_lo = true;
+    }
+    if (!have_lo || (!have_hi && (n & 1) == 0)) {                                         // uniform, rare
+        float xs[NK], res[3];
+#pragma unroll
+        for (int i = 0; i < NK; ++i) xs[i] = x[i];
+        lq_median_slow<NT, NK, CAP, BP>(xs, elig, n, have_lo, lo, b, hist, sh, list, redbuf, res);
+        lo = res[0]; hi = res[1]; b = res[2];
+    }
+    if (n & 1) hi = lo;
     lo_out = lo; hi_out = hi;
+    // next frame's window: centred on this median (a wild value just costs that frame a relocation)
+    const float nb = __fsub_rn(0.5f, __fmul_rn(psr_mid(lo, hi), LQ_A));
+    bcen = fabsf(nb) < 1.0e6f ? nb : 0.5f;
     return true;
 }
 
@@ -1049,9 +1169,11 @@ __global__ void __launch_bounds__(NT, MINB)
 cm_banks_epix_fi_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c, int nframes, int fpc)
 {
     constexpr int ROWS = 352, COLS = 384, NB = 8, TR = ROWS / 2, TC = COLS / NB, CH = TC / 8, NCH = TR * CH, CPT = NCH / NT, NK = CPT * 8;
-    constexpr int NW = NT / 32, CAP = NT / 4 * 4;
-    static_assert(NCH % NT == 0 && NT % 32 == 0 && NK <= 32, "tile must split evenly over the CTA");
+    constexpr int CAP = NT / 4 * 4;
+    using BP = BitsEpixWords;
+    static_assert(NCH % NT == 0 && NT % 32 == 0 && CPT <= 3, "tile must split evenly over the CTA; bit planes hold 3 chunks");
     extern __shared__ float4 sm4[];                               // [4][NCH]: ped0 px0-3, ped0 px4-7, ped1 px0-3, ped1 px4-7
+    int* sgp = reinterpret_cast<int*>(sm4 + 4 * NCH);             // [CPT][NT] first pixel of a thread's chunk; IMG: + [CPT][NT] its image index
     __shared__ int redbuf[64];
     __shared__ __align__(16) uint32_t hist[LQ_NB];
     __shared__ __align__(16) float list[CAP + 4];
@@ -1065,14 +1187,14 @@ cm_banks_epix_fi_kernel(const uint16_t* __restrict__ raw, float* __restrict__ ou
     const int f_begin = blockIdx.y * fpc, f_end = min(nframes, f_begin + fpc);
 
     for (int i = tid; i < LQ_NB; i += NT) hist[i] = 0u;
-    int gpj[CPT];
-    uint32_t mbits = 0, kbits = 0, e0bits = 0, e1bits = 0;        // bit q = pixel q of this thread
+    uint32_t kbits = 0, e0bits = 0, e1bits = 0;                   // bit BP::pos(i) = value i of this thread
+    uint32_t kinds = 0;                                           // IMG: where each chunk goes in the assembled image is the same for every frame
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
         const int ch = tid + j * NT;
         const int r = ch / CH, cc = ch - r * CH;
         const int gp = ((seg * ROWS + half * TR + r) * COLS) + bank * TC + cc * 8;
-        gpj[j] = gp;
+        sgp[j * NT + tid] = gp;
         sm4[0 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped0 + gp));
         sm4[1 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped0 + gp) + 1);
         sm4[2 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped1 + gp));
@@ -1081,80 +1203,349 @@ cm_banks_epix_fi_kernel(const uint16_t* __restrict__ raw, float* __restrict__ ou
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const uint32_t fb = ((i < 4 ? f.x : f.y) >> (8 * (i & 3))) & 0xFFu;
-            const int q = j * 8 + i;
-            mbits |= ((fb & PSR_FL_MASK) ? 1u : 0u) << q;
+            const int q = BP::pos(j * 8 + i);
             kbits |= ((fb & PSR_FL_KEEP) ? 1u : 0u) << q;
             e0bits |= ((fb & PSR_FL_ELIG0) ? 1u : 0u) << q;
             e1bits |= ((fb & PSR_FL_ELIG1) ? 1u : 0u) << q;
         }
+        if constexpr (IMG) {
+            int t0; kinds |= img_chunk_kind<8>(c.fwd + gp, t0) << (2 * j);
+            sgp[(CPT + j) * NT + tid] = t0;
+        }
     }
-    if (c.ignore_keep) kbits = 0xFFFFFFFFu;
-    // IMG: where each chunk goes in the assembled image is the same for every frame
-    int t0j[IMG ? CPT : 1]; uint32_t kinds = 0;
-    if constexpr (IMG) {
-#pragma unroll
-        for (int j = 0; j < CPT; ++j) kinds |= img_chunk_kind<8>(c.fwd + gpj[j], t0j[j]) << (2 * j);
-    }
+    const bool use_keep = c.has_keep && !c.ignore_keep;           // uniform: np.where(keep, v, 0) only when a keep mask is installed
     const size_t fout = IMG ? (size_t)c.H * c.W : (size_t)c.npix;
+    // always 0 (this kernel is epix10ka's), but not to the compiler: lets a value be made to depend on another, which
+    // keeps ptxas from hoisting every chunk's loads to the top and spilling the values it has already computed
+    const uint32_t zero = (uint32_t)c.det_kind;
     __syncthreads();
 
-    BlockRed<NW> red{redbuf, 0};
-    int cs = 0;                                                   // histogram centre * 32: the previous frame's median
+    float bcen = 0.5f;                                            // histogram window centred on 0, then on the previous frame's median
     for (int frame = f_begin; frame < f_end; ++frame) {
         const uint16_t* rawf = raw + (size_t)frame * c.npix;
         float* outf = out + (size_t)frame * fout;
         float x[NK];
-        uint32_t sbits = 0;                                       // bit q = data bit 14 of pixel q
+        uint32_t sbits = 0;                                       // bit BP::pos(i) = data bit 14 of value i
+        asm volatile("" : "+r"(kbits));                           // not loop-invariant to the compiler: it would hoist (and spill) 24 single-bit tests
+        uint4 rv[CPT];
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) rv[j] = __ldcs(reinterpret_cast<const uint4*>(rawf + sgp[j * NT + tid]));
+        uint32_t chain = 0;
 #pragma unroll
         for (int j = 0; j < CPT; ++j) {
-            const int ch = tid + j * NT;
-            const uint4 rv = __ldcs(reinterpret_cast<const uint4*>(rawf + gpj[j]));
-            const uint32_t w[4] = {rv.x, rv.y, rv.z, rv.w};
+            const int ch = tid + j * NT + (int)chain;             // chunk j's pedestals are fetched once chunk j - 1 is done
+            const uint32_t w[4] = {rv[j].x, rv[j].y, rv[j].z, rv[j].w};
             const float4 a0 = sm4[0 * NCH + ch], a1 = sm4[1 * NCH + ch], b0 = sm4[2 * NCH + ch], b1 = sm4[3 * NCH + ch];
             const float pa[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
             const float pb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int q = j * 8 + i;
-                const uint32_t v = (i & 1) ? (w[i >> 1] >> 16) : w[i >> 1];
-                const bool sel = (v & 0x4000u) != 0;
-                x[q] = __fsub_rn((float)(v & 0x3FFFu), sel ? pb[i] : pa[i]);
-                if (sel) sbits |= 1u << q;
+            for (int k = 0; k < 4; ++k) {
+                // both bit-14 flags of the word with one shift: bit 14 -> 4j + k, bit 30 -> 16 + 4j + k
+                sbits |= (w[k] >> (14 - 4 * j - k)) & (0x00010001u << (4 * j + k));
+#if PSR_CMF_MAGIC
+                const uint32_t wm = w[k] & 0x3FFF3FFFu;
+                // float(v) without a conversion: 0x4B000000 | v is 2^23 + v; both subtractions are exact or correctly rounded
+                const float fe = __fsub_rn(__uint_as_float(__byte_perm(wm, 0x4B000000u, 0x7610)), 8388608.0f);
+                const float fo = __fsub_rn(__uint_as_float(__byte_perm(wm, 0x4B000000u, 0x7632)), 8388608.0f);
+#else
+                const float fe = (float)(w[k] & 0x3FFFu), fo = (float)((w[k] >> 16) & 0x3FFFu);
+#endif
+                x[j * 8 + 2 * k] = psr_sub_sel(fe, pa[2 * k], pb[2 * k], w[k] & 0x4000u);
+                x[j * 8 + 2 * k + 1] = psr_sub_sel(fo, pa[2 * k + 1], pb[2 * k + 1], w[k] & 0x40000000u);
             }
+#if PSR_CMF_CHAIN
+            chain = __float_as_uint(x[j * 8 + 7]) & zero;
+#endif
         }
         const uint32_t elig = (sbits & e1bits) | (~sbits & e0bits);
 
-        // common_mode_2d: skip if n < npix_min, skip if |cm| > cormax
+        // common_mode_2d: skip if n < npix_min, skip if |cm| > cormax.  An unapplied correction is cm = +0: x - 0 == x for every x.
         float lo, hi, cm = 0.f;
-        if (block_median_linear<NT, NK, CAP>(x, elig, c.npix_min, cs, hist, selsh, list, red, lo, hi)) {      // uniform
+        if (block_median_linear<NT, NK, CAP, BP>(x, elig, c.npix_min, bcen, hist, selsh, list, redbuf, lo, hi)) {      // uniform
             const float med = psr_mid(lo, hi);
             if (!(fabsf(med) > c.cormax)) cm = med;
-            const float t = fminf(fmaxf(__fmul_rn(med, LQ_SCALE), -(float)LQ_CS_MAX), (float)LQ_CS_MAX);
-            cs = __float2int_rn(t);
         }
-        // an unapplied correction is cm = +0: x - 0 == x exactly, for every x
 
+        chain = 0;
 #pragma unroll
         for (int j = 0; j < CPT; ++j) {
-            const int gp = gpj[j];
+            const int gp = sgp[j * NT + tid] + (int)chain;        // one chunk's gain factors in registers at a time
             float o[8];
+            // the mask is folded into the gain factors (psr_set_constants): a masked pixel's factor is +-0
+            float g0[8], g1[8];
+            ld8(c.gf0 + gp, g0); ld8(c.gf1 + gp, g1);
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const float4 ga = __ldg(reinterpret_cast<const float4*>(c.gf0 + gp) + h), gb = __ldg(reinterpret_cast<const float4*>(c.gf1 + gp) + h);
+            for (int i = 0; i < 8; ++i) {
+                const int q = BP::pos(j * 8 + i);
+                const float xv = psr_sub_if(x[j * 8 + i], cm, elig & (1u << q));
+                o[i] = psr_mul_sel(xv, g0[i], g1[i], sbits & (1u << q));
+            }
+            if (use_keep) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) if (!(kbits & (1u << BP::pos(j * 8 + i)))) o[i] = 0.0f;
+            }
+#if PSR_CMF_CHAIN
+            chain = __float_as_uint(o[7]) & zero;
+#endif
+            if constexpr (IMG) img_store_chunk<8>(outf, c.fwd + gp, (kinds >> (2 * j)) & 3u, sgp[(CPT + j) * NT + tid], o);
+            else {
+                __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
+                __stcs(reinterpret_cast<float4*>(outf + gp + 4), make_float4(o[4], o[5], o[6], o[7]));
+            }
+        }
+    }
+}
+
+// =================================================================================================
+// epix10ka, mode 4, FRAME PAIRS: one 704-thread CTA per SM owns one bank tile and walks `fpc` frames of the
+// batch two at a time.  ALL of the tile's constants (both pedestal and both gain-factor entries, 135 KB)
+// are staged once in shared memory -- a thread only ever reads the slots of its own 12 pixels, so no
+// barrier guards them -- so the frame loop's global traffic is raw in and floats out, nothing else.  A
+// thread holds 12 pixels of each of the two frames (24 values, as floats, from load to store) and the
+// per-pixel flag bits as register planes.  Two frames per pass through the phases (histogram, scan,
+// collect, rank) halves the barriers per frame, doubles the independent work between them and lets the
+// two scans and the two rankings run on different warps at the same time.
+// =================================================================================================
+// value i = pixel (2k + h) of 4-pixel chunk j (i = 4j + 2k + h: word k of the chunk's two raw words, low / high half):
+// bit 2j + k + 16h, the place where ONE shift of the raw word drops its two bit-14 flags
+struct BitsEpixWords4 { static __device__ __forceinline__ constexpr int pos(int i) { return 2 * (i >> 2) + ((i & 3) >> 1) + 16 * (i & 1); } };
+
+template <bool IMG>
+__global__ void __launch_bounds__(704, 1)
+cm_banks_epix_pair_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c, int nframes, int fpc)
+{
+    constexpr int NT = 704, NF = 2, ROWS = 352, COLS = 384, NB = 8, TR = ROWS / 2, TC = COLS / NB, CH = TC / 4, NCH = TR * CH, CPT = NCH / NT, NK = CPT * 4;
+    constexpr int CAP = NT / NF, NSCAN = LQ_NB / 8;
+    using BP = BitsEpixWords4;
+    static_assert(NCH % NT == 0 && NT >= NF * NSCAN && CAP % 4 == 0, "tile / scan / rank layout");
+    extern __shared__ float4 sm4[];                               // [4][NCH]: ped0, ped1, gf0, gf1 of the 4 pixels of a chunk
+    int* sgp = reinterpret_cast<int*>(sm4 + 4 * NCH);             // [CPT][NT] first pixel of a thread's chunk; IMG: + [CPT][NT] its image index
+    __shared__ int redbuf[64];
+    __shared__ __align__(16) uint32_t hist[NF][LQ_NB];
+    __shared__ __align__(16) float list[NF][CAP + 4];
+    __shared__ __align__(16) int selsh[NF][48];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int bid = blockIdx.x;
+    const int bank = bid % NB; bid /= NB;
+    const int half = bid & 1;  bid >>= 1;
+    const int seg = bid;
+    const int f_begin = blockIdx.y * fpc, f_end = min(nframes, f_begin + fpc);
+
+    for (int i = tid; i < NF * LQ_NB; i += NT) (&hist[0][0])[i] = 0u;
+    uint32_t kbits = 0, e0bits = 0, e1bits = 0;                   // bit BP::pos(i) = value i of this thread
+    uint32_t kinds = 0;                                           // IMG: where each chunk goes in the assembled image is the same for every frame
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+        const int ch = tid + j * NT;
+        const int r = ch / CH, cc = ch - r * CH;
+        const int gp = ((seg * ROWS + half * TR + r) * COLS) + bank * TC + cc * 4;
+        sgp[j * NT + tid] = gp;
+        // the mask is folded into the gain factors (psr_set_constants): a masked pixel's factor is +-0
+        sm4[0 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped0 + gp));
+        sm4[1 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped1 + gp));
+        sm4[2 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.gf0 + gp));
+        sm4[3 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.gf1 + gp));
+        const uint32_t f = __ldg(reinterpret_cast<const uint32_t*>(c.flags + gp));
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t fb = (f >> (8 * i)) & 0xFFu;
+            const int q = BP::pos(j * 4 + i);
+            kbits |= ((fb & PSR_FL_KEEP) ? 1u : 0u) << q;
+            e0bits |= ((fb & PSR_FL_ELIG0) ? 1u : 0u) << q;
+            e1bits |= ((fb & PSR_FL_ELIG1) ? 1u : 0u) << q;
+        }
+        if constexpr (IMG) {
+            int t0; kinds |= img_chunk_kind<4>(c.fwd + gp, t0) << (2 * j);
+            sgp[(CPT + j) * NT + tid] = t0;
+        }
+    }
+    const bool use_keep = c.has_keep && !c.ignore_keep;           // uniform: np.where(keep, v, 0) only when a keep mask is installed
+    const size_t fout = IMG ? (size_t)c.H * c.W : (size_t)c.npix;
+    __syncthreads();
+
+    float bcen[NF];                                               // histogram windows: centred on 0, then on the previous median of the same slot
+#pragma unroll
+    for (int f = 0; f < NF; ++f) bcen[f] = 0.5f;
+    for (int frame = f_begin; frame < f_end; frame += NF) {
+        const bool pair = frame + 1 < f_end;                      // an odd tail runs its frame twice and stores it once
+        float x[NF][NK];
+        uint32_t sbits[NF], elig[NF];
+        asm volatile("" : "+r"(kbits));                           // not loop-invariant to the compiler: it would hoist (and spill) the single-bit tests
+#pragma unroll
+        for (int f = 0; f < NF; ++f) {
+            const uint16_t* rawf = raw + (size_t)(frame + ((f == 1 && pair) ? 1 : 0)) * c.npix;
+            uint2 rv[CPT];
+#pragma unroll
+            for (int j = 0; j < CPT; ++j) rv[j] = __ldcs(reinterpret_cast<const uint2*>(rawf + sgp[j * NT + tid]));
+            if (f == 0 && frame + NF < f_end) {                   // next pair's raw tiles on their way into L2 meanwhile
+#pragma unroll
+                for (int j = 0; j < CPT; ++j) {
+                    asm volatile("prefetch.global.L2 [%0];" :: "l"(rawf + (size_t)NF * c.npix + sgp[j * NT + tid]));
+                    asm volatile("prefetch.global.L2 [%0];" :: "l"(rawf + (size_t)(NF + 1) * c.npix + sgp[j * NT + tid]));
+                }
+            }
+            uint32_t sb = 0;
+#pragma unroll
+            for (int j = 0; j < CPT; ++j) {
+                const int ch = tid + j * NT;
+                const uint32_t w[2] = {rv[j].x, rv[j].y};
+                const float4 p0 = sm4[0 * NCH + ch], p1 = sm4[1 * NCH + ch];
+                const float pa[4] = {p0.x, p0.y, p0.z, p0.w}, pb[4] = {p1.x, p1.y, p1.z, p1.w};
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    // both bit-14 flags of the word with one shift: bit 14 -> 2j + k, bit 30 -> 16 + 2j + k
+                    sb |= (w[k] >> (14 - 2 * j - k)) & (0x00010001u << (2 * j + k));
+                    const uint32_t wm = w[k] & 0x3FFF3FFFu;
+                    // float(v) without a conversion: 0x4B000000 | v is 2^23 + v; both subtractions are exact or correctly rounded
+                    const float fe = __fsub_rn(__uint_as_float(__byte_perm(wm, 0x4B000000u, 0x7610)), 8388608.0f);
+                    const float fo = __fsub_rn(__uint_as_float(__byte_perm(wm, 0x4B000000u, 0x7632)), 8388608.0f);
+                    x[f][j * 4 + 2 * k] = psr_sub_sel(fe, pa[2 * k], pb[2 * k], w[k] & 0x4000u);
+                    x[f][j * 4 + 2 * k + 1] = psr_sub_sel(fo, pa[2 * k + 1], pb[2 * k + 1], w[k] & 0x40000000u);
+                }
+            }
+            sbits[f] = sb;
+            elig[f] = (sb & e1bits) | (~sb & e0bits);
+        }
+
+        // ---- the two medians (common_mode_2d: skip if n < npix_min, skip if |cm| > cormax) -------------------------
+        // histograms
+#pragma unroll
+        for (int f = 0; f < NF; ++f) {
+            const uint32_t cadd = (uint32_t)__cvta_generic_to_shared(&hist[f][0]) - 0x2C000000u;      // bits(2^23) * 4 mod 2^32
+#pragma unroll
+            for (int i = 0; i < NK; ++i) {
+                const uint32_t ad = lq_bits(x[f][i], LQ_A, bcen[f]) * 4u + cadd;
+                const uint32_t m = (elig[f] << (31 - BP::pos(i))) >> 31;                              // ineligible: add 0 (no branch around the atomic)
+                asm volatile("red.shared.add.u32 [%0], %1;" :: "r"(ad), "r"(m) : "memory");
+            }
+        }
+        __syncthreads();
+        // scans: warps 0-7 take frame 0's bins, warps 8-15 frame 1's
+        const int sf = warp >> 3, st = tid - sf * NSCAN;          // scanning frame / thread within the scan (valid for warp < 16)
+        uint32_t bn[8]; uint32_t ssum = 0, incl = 0;
+        if (warp < NF * (NSCAN / 32)) {
+            uint4* h4 = reinterpret_cast<uint4*>(&hist[sf][0]) + 2 * st;
+            const uint4 u = h4[0], v = h4[1];
+            h4[0] = make_uint4(0, 0, 0, 0); h4[1] = make_uint4(0, 0, 0, 0);                           // the owner leaves its bins zero
+            bn[0] = u.x; bn[1] = u.y; bn[2] = u.z; bn[3] = u.w; bn[4] = v.x; bn[5] = v.y; bn[6] = v.z; bn[7] = v.w;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) ssum += bn[j];
+            incl = ssum;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+            if (lane == 31) selsh[sf][warp & 7] = (int)incl;
+        }
+        __syncthreads();
+        if (warp < NF * (NSCAN / 32)) {
+            const int4 t0 = reinterpret_cast<const int4*>(&selsh[sf][0])[0], t1 = reinterpret_cast<const int4*>(&selsh[sf][0])[1];
+            const int tw[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+            int n = 0; uint32_t base = 0;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) { n += tw[w]; base += (w < (warp & 7)) ? (uint32_t)tw[w] : 0u; }
+            const int k1 = (n - 1) >> 1;
+            const uint32_t excl = base + incl - ssum;
+            if (n > 0 && (uint32_t)k1 >= excl && (uint32_t)k1 < excl + ssum) {
+                uint32_t rr = (uint32_t)k1 - excl; bool done = false;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (!done) { if (rr < bn[j]) { selsh[sf][32] = 8 * st + j; selsh[sf][33] = (int)rr; selsh[sf][34] = (int)bn[j]; done = true; } else rr -= bn[j]; }
+            }
+            if (st == 0) { selsh[sf][35] = 0; selsh[sf][36] = n; }
+        }
+        __syncthreads();
+        // collect the members of the two bins
+        int nn[NF], Bf[NF], rf[NF], Mf[NF]; bool fast[NF];
+#pragma unroll
+        for (int f = 0; f < NF; ++f) {
+            nn[f] = selsh[f][36]; Bf[f] = selsh[f][32]; rf[f] = selsh[f][33]; Mf[f] = selsh[f][34];
+            fast[f] = nn[f] >= c.npix_min && nn[f] >= 1 && Bf[f] > 0 && Bf[f] < LQ_NB - 1 && Mf[f] <= CAP;     // uniform
+            if (fast[f]) {
+                const uint32_t target = 0x4B000000u + (uint32_t)Bf[f];
+                uint32_t hits = 0; float cand = 0.f;
+                float bb = bcen[f];
+                asm volatile("" : "+f"(bb));                      // the bins are recomputed, not kept from the histogram pass (12 registers)
+#pragma unroll
+                for (int i = 0; i < NK; ++i)
+                    if (lq_bits(x[f][i], LQ_A, bb) == target) { hits |= 1u << BP::pos(i); cand = x[f][i]; }
+                // a thread almost never holds two members of the bin: one candidate register, one branch per thread
+                if (hits != 0u) {
+                    if ((hits & (hits - 1u)) == 0u) { if (hits & elig[f]) list[f][atomicAdd(&selsh[f][35], 1)] = cand; }
+                    else {
+                        hits &= elig[f];
+#pragma unroll
+                        for (int i = 0; i < NK; ++i) if (hits & (1u << BP::pos(i))) list[f][atomicAdd(&selsh[f][35], 1)] = x[f][i];
+                    }
+                }
+                if (tid < 4) list[f][Mf[f] + tid] = __int_as_float(0x7f800000);                       // pad to a multiple of four
+            }
+        }
+        __syncthreads();
+        // rank: threads [0, M0) take frame 0's list, threads [CAP, CAP + M1) frame 1's
+        {
+            const int f = tid >= CAP ? 1 : 0, t = tid - f * CAP;
+            if (fast[f] && t < Mf[f]) {
+                const float v = list[f][t];
+                const int r = rf[f];
+                int lt = 0, le = 0;
+                for (int j = 0; j < Mf[f]; j += 4) {
+                    const float4 u = *reinterpret_cast<const float4*>(&list[f][j]);
+                    lt += (u.x < v) + (u.y < v) + (u.z < v) + (u.w < v);
+                    le += (u.x <= v) + (u.y <= v) + (u.z <= v) + (u.w <= v);
+                }
+                if (lt <= r && r < le) selsh[f][37] = __float_as_int(v);
+                if (lt <= r + 1 && r + 1 < le) selsh[f][38] = __float_as_int(v);
+            }
+        }
+        __syncthreads();
+        float cm[NF];
+#pragma unroll
+        for (int f = 0; f < NF; ++f) {
+            cm[f] = 0.f;                                          // an unapplied correction is cm = +0: x - 0 == x for every x
+            if (nn[f] >= c.npix_min && nn[f] >= 1) {              // uniform
+                float lo = __int_as_float(selsh[f][37]);
+                const bool have_hi = rf[f] + 1 < Mf[f];
+                float hi = have_hi ? __int_as_float(selsh[f][38]) : lo;
+                if (!fast[f] || (!have_hi && (nn[f] & 1) == 0)) { // uniform, rare: everything unusual, on a copy in local memory
+                    float xs[NK], res[3];
+#pragma unroll
+                    for (int i = 0; i < NK; ++i) xs[i] = x[f][i];
+                    lq_median_slow<NT, NK, CAP, BP>(xs, elig[f], nn[f], fast[f], lo, bcen[f], &hist[f][0], &selsh[f][0], &list[f][0], redbuf, res);
+                    lo = res[0]; hi = res[1];
+                }
+                if (nn[f] & 1) hi = lo;
+                const float med = psr_mid(lo, hi);
+                if (!(fabsf(med) > c.cormax)) cm[f] = med;
+                const float nb = __fsub_rn(0.5f, __fmul_rn(med, LQ_A));       // next window: centred on this median
+                bcen[f] = fabsf(nb) < 1.0e6f ? nb : 0.5f;
+            }
+        }
+
+        // ---- gain, keep, store ---------------------------------------------------------------------------------------
+#pragma unroll
+        for (int f = 0; f < NF; ++f) {
+            if (f == 1 && !pair) break;
+            float* outf = out + (size_t)(frame + f) * fout;
+#pragma unroll
+            for (int j = 0; j < CPT; ++j) {
+                const int ch = tid + j * NT;
+                const float4 ga = sm4[2 * NCH + ch], gb = sm4[3 * NCH + ch];
                 const float g0[4] = {ga.x, ga.y, ga.z, ga.w}, g1[4] = {gb.x, gb.y, gb.z, gb.w};
+                float o[8];
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const int q = j * 8 + h * 4 + i;
-                    float xv = x[q];
-                    if (elig & (1u << q)) xv = __fsub_rn(xv, cm);
-                    const float gf = (sbits & (1u << q)) ? g1[i] : g0[i];
-                    float v = __fmul_rn(xv, gf);
-                    v = __fmul_rn(v, (mbits & (1u << q)) ? 1.0f : 0.0f);
-                    o[h * 4 + i] = (kbits & (1u << q)) ? v : 0.0f;
+                    const int q = BP::pos(j * 4 + i);
+                    const float xv = psr_sub_if(x[f][j * 4 + i], cm[f], elig[f] & (1u << q));
+                    o[i] = psr_mul_sel(xv, g0[i], g1[i], sbits[f] & (1u << q));
                 }
-                if constexpr (!IMG) __stcs(reinterpret_cast<float4*>(outf + gp) + h, make_float4(o[h * 4], o[h * 4 + 1], o[h * 4 + 2], o[h * 4 + 3]));
+                if (use_keep) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) if (!(kbits & (1u << BP::pos(j * 4 + i)))) o[i] = 0.0f;
+                }
+                const int gp = sgp[j * NT + tid];
+                if constexpr (IMG) img_store_chunk<4>(outf, c.fwd + gp, (kinds >> (2 * j)) & 3u, sgp[(CPT + j) * NT + tid], o);
+                else __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
             }
-            if constexpr (IMG) img_store_chunk<8>(outf, c.fwd + gp, (kinds >> (2 * j)) & 3u, t0j[j], o);
         }
     }
 }
@@ -1174,10 +1565,17 @@ constexpr int EPIX_NT = 352, JF_NT = 512;
 #endif
 constexpr size_t EPIX_SMEM = ((size_t)(176 * 49) * 5 + 15) / 16 * 16 + (EPIX_NT / 32) * 4 * 256 * 4;   // padded tile (float + flag byte) + warp histograms
 constexpr size_t JF_SMEM = ((size_t)(256 * 65) * 5 + 15) / 16 * 16 + (JF_NT / 32) * 4 * 256 * 4;
-constexpr size_t EPIX_FI_SMEM = (size_t)1056 * (4 * 16);         // pedestals of one bank tile
+constexpr size_t EPIX_FI_SMEM = (size_t)1056 * (4 * 16) + (size_t)6 * 352 * 4;   // pedestals of one bank tile + per-thread chunk offsets
 #ifndef PSR_CM_FPC
 #define PSR_CM_FPC 8           /* frames per CTA of the frames-inner common-mode kernel */
 #endif
+#ifndef PSR_CM_PAIR
+#define PSR_CM_PAIR 1          /* epix10ka bank medians: 1 = frame-pair kernel (704 threads, all constants in shared memory) */
+#endif
+#ifndef PSR_CM_PAIR_FPC
+#define PSR_CM_PAIR_FPC 16     /* frames per CTA of the frame-pair kernel */
+#endif
+constexpr size_t EPIX_PAIR_SMEM = (size_t)2112 * (4 * 16) + (size_t)6 * 704 * 4;   // all four constant tables of one bank tile + per-thread chunk offsets
 
 }  // namespace
 
@@ -1192,6 +1590,10 @@ cudaError_t psr_common_mode_setup(void)
         e = cudaFuncSetAttribute(cm_banks_kernel<1, 512, 1024, 16, PSR_CMB_JF_NT, PSR_CMB_JF_MINB, PSR_CMB_JF_CW, PSR_CMB_JF_KS != 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * 64 * 4);
         if (e != cudaSuccess) return e;
     }
+    e = cudaFuncSetAttribute(cm_banks_epix_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_PAIR_SMEM);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(cm_banks_epix_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_PAIR_SMEM);
+    if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(cm_banks_epix_fi_kernel<EPIX_NT, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_FI_SMEM);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(cm_banks_epix_fi_kernel<EPIX_NT, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_FI_SMEM);
@@ -1205,7 +1607,11 @@ template <bool IMG>
 cudaError_t launch_banks(const PsrDev& c, const uint16_t* d_raw, int nframes, float* d_out, cudaStream_t st)
 {
     if (c.det_kind == 0) {
-        if (PSR_CM_FPC > 1 && nframes > 1) {
+        if (PSR_CM_PAIR && nframes > 1) {
+            const int fpc = PSR_CM_PAIR_FPC;
+            dim3 g2((unsigned)c.nseg * 2 * 8, (unsigned)((nframes + fpc - 1) / fpc));
+            cm_banks_epix_pair_kernel<IMG><<<g2, 704, EPIX_PAIR_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
+        } else if (PSR_CM_FPC > 1 && nframes > 1) {
             const int fpc = PSR_CM_FPC;
             dim3 g2((unsigned)c.nseg * 2 * 8, (unsigned)((nframes + fpc - 1) / fpc));
             cm_banks_epix_fi_kernel<EPIX_NT, 2, IMG><<<g2, EPIX_NT, EPIX_FI_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);

@@ -34,6 +34,7 @@ struct PsrDev {
     // common mode
     int cm_mode; float cormax; int npix_min; uint32_t elig_mask;
     int ignore_keep;               // 1: calib-layout keep mask not applied (image mode masks the 2-D image)
+    int has_keep;                  // 1: a calib-layout keep mask is installed (else every flag byte has PSR_FL_KEEP set)
 };
 
 // launchers (each returns the launch's cudaError_t)
