@@ -47,6 +47,15 @@
 #ifndef PSR_LQ_ATOM             /* histogram update: 1 = unconditional add of 0/1, 0 = increment under a branch */
 #define PSR_LQ_ATOM 1
 #endif
+#ifndef PSR_PAIR_NF              /* frame-pair kernel: frames per pass (2, or 1 for comparison) */
+#define PSR_PAIR_NF 2
+#endif
+#ifndef PSR_PAIR_STAGE           /* frame-pair kernel: next pair's raw tiles staged in shared memory by cp.async */
+#define PSR_PAIR_STAGE 0
+#endif
+#ifndef PSR_PAIR_PREFETCH        /* frame-pair kernel: next pair's raw tiles prefetched into L2 */
+#define PSR_PAIR_PREFETCH 1
+#endif
 #ifndef PSR_CM_MATCH
 #define PSR_CM_MATCH 0
 #endif
@@ -466,6 +475,11 @@ __device__ __forceinline__ void block_median_keys(const K& key, uint32_t elig, i
         }
     }
     lo_out = lo; hi_out = hi;
+}
+
+// 8 bytes global -> shared, asynchronously, past L1
+__device__ __forceinline__ void psr_cp_async8(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
 }
 
 // Selects written as a predicated second operation: the arithmetic runs on the FMA pipe, which has room, instead
@@ -1310,16 +1324,17 @@ cm_banks_epix_fi_kernel(const uint16_t* __restrict__ raw, float* __restrict__ ou
 // bit 2j + k + 16h, the place where ONE shift of the raw word drops its two bit-14 flags
 struct BitsEpixWords4 { static __device__ __forceinline__ constexpr int pos(int i) { return 2 * (i >> 2) + ((i & 3) >> 1) + 16 * (i & 1); } };
 
-template <bool IMG>
+template <bool IMG, int NF>
 __global__ void __launch_bounds__(704, 1)
 cm_banks_epix_pair_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c, int nframes, int fpc)
 {
-    constexpr int NT = 704, NF = 2, ROWS = 352, COLS = 384, NB = 8, TR = ROWS / 2, TC = COLS / NB, CH = TC / 4, NCH = TR * CH, CPT = NCH / NT, NK = CPT * 4;
+    constexpr int NT = 704, ROWS = 352, COLS = 384, NB = 8, TR = ROWS / 2, TC = COLS / NB, CH = TC / 4, NCH = TR * CH, CPT = NCH / NT, NK = CPT * 4;
     constexpr int CAP = NT / NF, NSCAN = LQ_NB / 8;
     using BP = BitsEpixWords4;
     static_assert(NCH % NT == 0 && NT >= NF * NSCAN && CAP % 4 == 0, "tile / scan / rank layout");
     extern __shared__ float4 sm4[];                               // [4][NCH]: ped0, ped1, gf0, gf1 of the 4 pixels of a chunk
     int* sgp = reinterpret_cast<int*>(sm4 + 4 * NCH);             // [CPT][NT] first pixel of a thread's chunk; IMG: + [CPT][NT] its image index
+    uint2* sraw = reinterpret_cast<uint2*>(sgp + 2 * CPT * NT);   // [NF][CPT][NT] the next pair's raw chunks, staged by cp.async (each thread its own)
     __shared__ int redbuf[64];
     __shared__ __align__(16) uint32_t hist[NF][LQ_NB];
     __shared__ __align__(16) float list[NF][CAP + 4];
@@ -1362,29 +1377,61 @@ cm_banks_epix_pair_kernel(const uint16_t* __restrict__ raw, float* __restrict__ 
     }
     const bool use_keep = c.has_keep && !c.ignore_keep;           // uniform: np.where(keep, v, 0) only when a keep mask is installed
     const size_t fout = IMG ? (size_t)c.H * c.W : (size_t)c.npix;
+#if PSR_PAIR_STAGE
+    if (f_begin < f_end) {                                        // the first pair's raw chunks
+#pragma unroll
+        for (int g = 0; g < NF; ++g) {
+            const int fr = min(f_begin + g, f_end - 1);
+#pragma unroll
+            for (int j = 0; j < CPT; ++j)
+                psr_cp_async8(&sraw[(g * CPT + j) * NT + tid], raw + (size_t)fr * c.npix + sgp[j * NT + tid]);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+#endif
     __syncthreads();
 
     float bcen[NF];                                               // histogram windows: centred on 0, then on the previous median of the same slot
 #pragma unroll
     for (int f = 0; f < NF; ++f) bcen[f] = 0.5f;
     for (int frame = f_begin; frame < f_end; frame += NF) {
-        const bool pair = frame + 1 < f_end;                      // an odd tail runs its frame twice and stores it once
+        const bool pair = NF > 1 && frame + 1 < f_end;            // an odd tail runs its frame twice and stores it once
         float x[NF][NK];
         uint32_t sbits[NF], elig[NF];
         asm volatile("" : "+r"(kbits));                           // not loop-invariant to the compiler: it would hoist (and spill) the single-bit tests
 #pragma unroll
         for (int f = 0; f < NF; ++f) {
-            const uint16_t* rawf = raw + (size_t)(frame + ((f == 1 && pair) ? 1 : 0)) * c.npix;
             uint2 rv[CPT];
+#if PSR_PAIR_STAGE
+            // this pair's raw chunks were staged in shared memory while the previous pair was processed (thread-private
+            // slots: the thread's own wait_group is all the ordering needed); then the next pair's copies are started
+            if (f == 0) asm volatile("cp.async.wait_group 0;" ::: "memory");
+#pragma unroll
+            for (int j = 0; j < CPT; ++j) rv[j] = sraw[(f * CPT + j) * NT + tid];
+            if (f == NF - 1 && frame + NF < f_end) {
+#pragma unroll
+                for (int g = 0; g < NF; ++g) {
+                    const int fr = min(frame + NF + g, f_end - 1);                // an odd tail stages its frame twice
+#pragma unroll
+                    for (int j = 0; j < CPT; ++j)
+                        psr_cp_async8(&sraw[(g * CPT + j) * NT + tid], raw + (size_t)fr * c.npix + sgp[j * NT + tid]);
+                }
+                asm volatile("cp.async.commit_group;" ::: "memory");
+            }
+#else
+            const uint16_t* rawf = raw + (size_t)(frame + ((f == 1 && pair) ? 1 : 0)) * c.npix;
 #pragma unroll
             for (int j = 0; j < CPT; ++j) rv[j] = __ldcs(reinterpret_cast<const uint2*>(rawf + sgp[j * NT + tid]));
+#if PSR_PAIR_PREFETCH
             if (f == 0 && frame + NF < f_end) {                   // next pair's raw tiles on their way into L2 meanwhile
 #pragma unroll
                 for (int j = 0; j < CPT; ++j) {
                     asm volatile("prefetch.global.L2 [%0];" :: "l"(rawf + (size_t)NF * c.npix + sgp[j * NT + tid]));
-                    asm volatile("prefetch.global.L2 [%0];" :: "l"(rawf + (size_t)(NF + 1) * c.npix + sgp[j * NT + tid]));
+                    if (NF > 1) asm volatile("prefetch.global.L2 [%0];" :: "l"(rawf + (size_t)(NF + 1) * c.npix + sgp[j * NT + tid]));
                 }
             }
+#endif
+#endif
             uint32_t sb = 0;
 #pragma unroll
             for (int j = 0; j < CPT; ++j) {
@@ -1483,18 +1530,21 @@ cm_banks_epix_pair_kernel(const uint16_t* __restrict__ raw, float* __restrict__ 
         __syncthreads();
         // rank: threads [0, M0) take frame 0's list, threads [CAP, CAP + M1) frame 1's
         {
-            const int f = tid >= CAP ? 1 : 0, t = tid - f * CAP;
-            if (fast[f] && t < Mf[f]) {
-                const float v = list[f][t];
-                const int r = rf[f];
+            const bool f1 = NF > 1 && tid >= CAP;
+            const int t = f1 ? tid - CAP : tid, M = f1 ? Mf[NF - 1] : Mf[0], r = f1 ? rf[NF - 1] : rf[0];
+            const bool on = f1 ? fast[NF - 1] : fast[0];
+            const float* lst = f1 ? &list[NF - 1][0] : &list[0][0];
+            int* shf = f1 ? &selsh[NF - 1][0] : &selsh[0][0];
+            if (on && t < M) {
+                const float v = lst[t];
                 int lt = 0, le = 0;
-                for (int j = 0; j < Mf[f]; j += 4) {
-                    const float4 u = *reinterpret_cast<const float4*>(&list[f][j]);
+                for (int j = 0; j < M; j += 4) {
+                    const float4 u = *reinterpret_cast<const float4*>(lst + j);
                     lt += (u.x < v) + (u.y < v) + (u.z < v) + (u.w < v);
                     le += (u.x <= v) + (u.y <= v) + (u.z <= v) + (u.w <= v);
                 }
-                if (lt <= r && r < le) selsh[f][37] = __float_as_int(v);
-                if (lt <= r + 1 && r + 1 < le) selsh[f][38] = __float_as_int(v);
+                if (lt <= r && r < le) shf[37] = __float_as_int(v);
+                if (lt <= r + 1 && r + 1 < le) shf[38] = __float_as_int(v);
             }
         }
         __syncthreads();
@@ -1575,7 +1625,7 @@ constexpr size_t EPIX_FI_SMEM = (size_t)1056 * (4 * 16) + (size_t)6 * 352 * 4;  
 #ifndef PSR_CM_PAIR_FPC
 #define PSR_CM_PAIR_FPC 16     /* frames per CTA of the frame-pair kernel */
 #endif
-constexpr size_t EPIX_PAIR_SMEM = (size_t)2112 * (4 * 16) + (size_t)6 * 704 * 4;   // all four constant tables of one bank tile + per-thread chunk offsets
+constexpr size_t EPIX_PAIR_SMEM = (size_t)2112 * (4 * 16) + (size_t)6 * 704 * 4 + (PSR_PAIR_STAGE ? (size_t)2 * 3 * 704 * 8 : 0);   // all four constant tables of one bank tile + per-thread chunk offsets + a pair of raw tiles
 
 }  // namespace
 
@@ -1590,9 +1640,9 @@ cudaError_t psr_common_mode_setup(void)
         e = cudaFuncSetAttribute(cm_banks_kernel<1, 512, 1024, 16, PSR_CMB_JF_NT, PSR_CMB_JF_MINB, PSR_CMB_JF_CW, PSR_CMB_JF_KS != 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * 64 * 4);
         if (e != cudaSuccess) return e;
     }
-    e = cudaFuncSetAttribute(cm_banks_epix_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_PAIR_SMEM);
+    e = cudaFuncSetAttribute(cm_banks_epix_pair_kernel<false, PSR_PAIR_NF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_PAIR_SMEM);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(cm_banks_epix_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_PAIR_SMEM);
+    e = cudaFuncSetAttribute(cm_banks_epix_pair_kernel<true, PSR_PAIR_NF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_PAIR_SMEM);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(cm_banks_epix_fi_kernel<EPIX_NT, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_FI_SMEM);
     if (e != cudaSuccess) return e;
@@ -1610,7 +1660,7 @@ cudaError_t launch_banks(const PsrDev& c, const uint16_t* d_raw, int nframes, fl
         if (PSR_CM_PAIR && nframes > 1) {
             const int fpc = PSR_CM_PAIR_FPC;
             dim3 g2((unsigned)c.nseg * 2 * 8, (unsigned)((nframes + fpc - 1) / fpc));
-            cm_banks_epix_pair_kernel<IMG><<<g2, 704, EPIX_PAIR_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
+            cm_banks_epix_pair_kernel<IMG, PSR_PAIR_NF><<<g2, 704, EPIX_PAIR_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
         } else if (PSR_CM_FPC > 1 && nframes > 1) {
             const int fpc = PSR_CM_FPC;
             dim3 g2((unsigned)c.nseg * 2 * 8, (unsigned)((nframes + fpc - 1) / fpc));
