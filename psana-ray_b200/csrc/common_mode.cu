@@ -50,11 +50,17 @@
 #ifndef PSR_PAIR_NF              /* frame-pair kernel: frames per pass (2, or 1 for comparison) */
 #define PSR_PAIR_NF 2
 #endif
+#ifndef PSR_PAIR_PARK            /* frame-pair kernel: the second frame's values wait in shared memory between the phases */
+#define PSR_PAIR_PARK 1
+#endif
 #ifndef PSR_PAIR_STAGE           /* frame-pair kernel: next pair's raw tiles staged in shared memory by cp.async */
 #define PSR_PAIR_STAGE 0
 #endif
 #ifndef PSR_PAIR_PREFETCH        /* frame-pair kernel: next pair's raw tiles prefetched into L2 */
 #define PSR_PAIR_PREFETCH 1
+#endif
+#ifndef PSR_CMF_OPAQUE
+#define PSR_CMF_OPAQUE 1
 #endif
 #ifndef PSR_CM_MATCH
 #define PSR_CM_MATCH 0
@@ -537,16 +543,54 @@ struct BitsLinear { static __device__ __forceinline__ constexpr int pos(int i) {
 // bit 4j + k + 16h, the place where ONE shift of the raw word drops its two bit-14 flags
 struct BitsEpixWords { static __device__ __forceinline__ constexpr int pos(int i) { return 4 * (i >> 3) + ((i & 7) >> 1) + 16 * (i & 1); } };
 
+// Who synchronises with whom: the whole CTA, or one of several equal groups of warps inside it, each on a hardware
+// barrier of its own (the groups then run their phases independently, like CTAs that share the tile's constants).
+struct CtaGroup {
+    __device__ __forceinline__ int tid() const { return threadIdx.x; }
+    __device__ __forceinline__ void sync() const { __syncthreads(); }
+};
+template <int N>
+struct WarpGroup {
+    int t, id;                                       // thread within the group; barrier 1 + group index
+    __device__ __forceinline__ int tid() const { return t; }
+    __device__ __forceinline__ void sync() const { asm volatile("bar.sync %0, %1;" :: "r"(id), "n"(N) : "memory"); }
+};
+// BlockRed over a group
+template <int NW, typename G>
+struct GroupRed {
+    int* buf; int phase; G g;
+    __device__ __forceinline__ int sum(int v) {
+        v = __reduce_add_sync(0xFFFFFFFFu, v);
+        if ((g.tid() & 31) == 0) buf[phase * 32 + (g.tid() >> 5)] = v;
+        g.sync();
+        int t = 0;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) t += buf[phase * 32 + w];
+        phase ^= 1;
+        return t;
+    }
+    __device__ __forceinline__ uint32_t minu(uint32_t v) {
+        v = __reduce_min_sync(0xFFFFFFFFu, v);
+        if ((g.tid() & 31) == 0) buf[phase * 32 + (g.tid() >> 5)] = (int)v;
+        g.sync();
+        uint32_t t = 0xFFFFFFFFu;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) t = min(t, (uint32_t)buf[phase * 32 + w]);
+        phase ^= 1;
+        return t;
+    }
+};
+
 struct LocalVals { const float* p; __device__ __forceinline__ float operator[](int i) const { return p[i]; } };
 
 // One histogram pass + scan: on return sh[32] = bin holding rank k1 = (n - 1) / 2, sh[33] = rank inside it, sh[34] = its
-// population, sh[36] = n (eligible values), sh[35] = 0; hist is zero again.  Every thread of the CTA must call it.
-template <int NT, int NK, typename BP, typename X>
-__device__ __forceinline__ void lq_pass(const X& x, uint32_t elig, float a, float b, uint32_t* hist, int* sh)
+// population, sh[36] = n (eligible values), sh[35] = 0; hist is zero again.  Every thread of the group must call it.
+template <int NT, int NK, typename BP, typename X, typename G>
+__device__ __forceinline__ void lq_pass(const X& x, uint32_t elig, float a, float b, uint32_t* hist, int* sh, const G& g)
 {
     constexpr int NSCAN = LQ_NB / 8;                 // threads that scan 8 bins each
     static_assert(NT >= NSCAN && NSCAN % 32 == 0, "scan layout");
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = g.tid(), lane = tid & 31, warp = tid >> 5;
     const uint32_t cadd = (uint32_t)__cvta_generic_to_shared(hist) - 0x2C000000u;        // bits(2^23) * 4 mod 2^32
 #pragma unroll
     for (int i = 0; i < NK; ++i) {
@@ -558,7 +602,7 @@ __device__ __forceinline__ void lq_pass(const X& x, uint32_t elig, float a, floa
         asm volatile("{ .reg .pred q; setp.ne.u32 q, %1, 0; @q red.shared.add.u32 [%0], 1; }" :: "r"(ad), "r"(elig & (1u << BP::pos(i))) : "memory");
 #endif
     }
-    __syncthreads();
+    g.sync();
     uint32_t bn[8]; uint32_t s = 0, incl = 0;
     if (tid < NSCAN) {
         uint4* h4 = reinterpret_cast<uint4*>(hist) + 2 * tid;
@@ -572,7 +616,7 @@ __device__ __forceinline__ void lq_pass(const X& x, uint32_t elig, float a, floa
         for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
         if (lane == 31) sh[warp] = (int)incl;
     }
-    __syncthreads();
+    g.sync();
     int n = 0; uint32_t base = 0;
     {
         const int4 t0 = reinterpret_cast<const int4*>(sh)[0], t1 = reinterpret_cast<const int4*>(sh)[1];
@@ -591,17 +635,17 @@ __device__ __forceinline__ void lq_pass(const X& x, uint32_t elig, float a, floa
         }
     }
     if (tid == NT - 1) { sh[35] = 0; sh[36] = n; }
-    __syncthreads();
+    g.sync();
 }
 
 // The members of bin B (fine window b) are collected and ranked by one thread each: lo = rank r, hi = rank r + 1 when
 // the bin holds it (have_hi).  sh[35] must be 0 on entry (lq_pass leaves it so); M <= CAP.  Every thread must call it.
-template <int NT, int NK, int CAP, typename BP, typename X>
+template <int NT, int NK, int CAP, typename BP, typename X, typename G>
 __device__ __forceinline__ void lq_collect_rank(const X& x, uint32_t elig, float b, int B, int r, int M, int* sh, float* list,
-                                                float& lo, float& hi, bool& have_hi)
+                                                float& lo, float& hi, bool& have_hi, const G& g)
 {
     static_assert(CAP <= NT && CAP % 4 == 0, "rank layout");
-    const int tid = threadIdx.x;
+    const int tid = g.tid();
     const uint32_t target = 0x4B000000u + (uint32_t)B;
     uint32_t hits = 0; float cand = 0.f;
     asm volatile("" : "+f"(b));                          // the bins are recomputed, not kept from the histogram pass (NK registers)
@@ -620,7 +664,7 @@ __device__ __forceinline__ void lq_collect_rank(const X& x, uint32_t elig, float
         }
     }
     if (tid < 4) list[M + tid] = __int_as_float(0x7f800000);                              // pad to a multiple of four
-    __syncthreads();
+    g.sync();
     if (tid < M) {
         const float v = list[tid];
         int lt = 0, le = 0;
@@ -632,7 +676,7 @@ __device__ __forceinline__ void lq_collect_rank(const X& x, uint32_t elig, float
         if (lt <= r && r < le) sh[37] = __float_as_int(v);
         if (lt <= r + 1 && r + 1 < le) sh[38] = __float_as_int(v);
     }
-    __syncthreads();
+    g.sync();
     lo = __int_as_float(sh[37]);
     have_hi = r + 1 < M;
     hi = have_hi ? __int_as_float(sh[38]) : lo;
@@ -645,35 +689,35 @@ __device__ __forceinline__ void lq_collect_rank(const X& x, uint32_t elig, float
 //   32 ADU per bin over +-32768 ADU, the fine window moved to the middle of the bin that pass finds, fine pass + ranking
 //   again.  What even that does not settle goes to a 32-step binary search on the float keys, one block-wide count per bit.
 // out[0] = lo, out[1] = hi, out[2] = the fine window's b as used (unchanged unless relocated).
-template <int NT, int NK, int CAP, typename BP>
+template <int NT, int NK, int CAP, typename BP, typename G>
 __device__ __noinline__ void lq_median_slow(const float* xs, uint32_t elig, int n, bool have_lo, float lo, float b,
-                                            uint32_t* hist, int* sh, float* list, int* redbuf, float* out)
+                                            uint32_t* hist, int* sh, float* list, int* redbuf, float* out, G g)
 {
     const LocalVals x{xs};
     const int k1 = (n - 1) >> 1, k2 = n >> 1;
     float hi = lo; bool have_hi = false;
-    __syncthreads();
+    g.sync();
     if (!have_lo) {
         int B = sh[32];
-        __syncthreads();
+        g.sync();
         if (B <= 0 || B >= LQ_NB - 1) {
-            lq_pass<NT, NK, BP>(x, elig, LQ_A_COARSE, 0.5f, hist, sh);
+            lq_pass<NT, NK, BP>(x, elig, LQ_A_COARSE, 0.5f, hist, sh, g);
             B = sh[32];
-            __syncthreads();
+            g.sync();
             if (B > 0 && B < LQ_NB - 1) {
                 const float xc = __fmul_rn(__fsub_rn(__fmul_rn((float)B + 0.5f, 1.0f / (float)(LQ_NB - 1)), 0.5f), 1.0f / LQ_A_COARSE);
                 b = __fsub_rn(0.5f, __fmul_rn(xc, LQ_A));
-                lq_pass<NT, NK, BP>(x, elig, LQ_A, b, hist, sh);
+                lq_pass<NT, NK, BP>(x, elig, LQ_A, b, hist, sh, g);
                 B = sh[32];
                 const int r = sh[33], M = sh[34];
                 if (B > 0 && B < LQ_NB - 1 && M <= CAP) {
-                    lq_collect_rank<NT, NK, CAP, BP>(x, elig, b, B, r, M, sh, list, lo, hi, have_hi);
+                    lq_collect_rank<NT, NK, CAP, BP>(x, elig, b, B, r, M, sh, list, lo, hi, have_hi, g);
                     have_lo = true;
                 }
             }
         }
         if (!have_lo) {
-            BlockRed<NT / 32> red{redbuf, 0};
+            GroupRed<NT / 32, G> red{redbuf, 0, g};
             uint32_t pre = 0;
 #pragma unroll 1
             for (int bit = 31; bit >= 0; --bit) {
@@ -684,20 +728,20 @@ __device__ __noinline__ void lq_median_slow(const float* xs, uint32_t elig, int 
                 cnt = red.sum(cnt);
                 if (cnt <= k1) pre = cand;
             }
-            __syncthreads();
+            g.sync();
             lo = psr_key2f(pre); hi = lo;
         }
     }
     if (k2 != k1 && !have_hi) {
         // the upper middle value: the smallest eligible value above lo, or lo itself when its duplicates reach rank k2
-        BlockRed<NT / 32> red{redbuf, 0};
+        GroupRed<NT / 32, G> red{redbuf, 0, g};
         int cle = 0; uint32_t mg = 0xFFFFFFFFu;
 #pragma unroll 1
         for (int i = 0; i < NK; ++i)
             if (elig & (1u << BP::pos(i))) { cle += (xs[i] <= lo); if (xs[i] > lo) mg = min(mg, psr_f2key(xs[i])); }
         cle = red.sum(cle);
         mg = red.minu(mg);
-        __syncthreads();
+        g.sync();
         hi = cle <= k2 ? psr_key2f(mg) : lo;
     }
     if (k2 == k1) hi = lo;
@@ -706,27 +750,27 @@ __device__ __noinline__ void lq_median_slow(const float* xs, uint32_t elig, int 
 
 // hist: LQ_NB words, all zero on entry and on exit; sh: 48 ints (16-byte aligned); list: CAP + 4 floats;
 // bcen: the window's b = 0.5 - centre / 64, updated to the median found.  Returns false (uniformly) when fewer than
-// max(npix_min, 1) values are eligible; else lo/hi = the two middle order statistics.  Every thread of the CTA must call it.
-template <int NT, int NK, int CAP, typename BP>
+// max(npix_min, 1) values are eligible; else lo/hi = the two middle order statistics.  Every thread of the group must call it.
+template <int NT, int NK, int CAP, typename BP, typename G>
 __device__ __forceinline__ bool block_median_linear(const float (&x)[NK], uint32_t elig, int npix_min, float& bcen,
                                                     uint32_t* hist, int* sh, float* list, int* redbuf,
-                                                    float& lo_out, float& hi_out)
+                                                    float& lo_out, float& hi_out, const G& g)
 {
     float b = bcen;
-    lq_pass<NT, NK, BP>(x, elig, LQ_A, b, hist, sh);
+    lq_pass<NT, NK, BP>(x, elig, LQ_A, b, hist, sh, g);
     const int n = sh[36];
     if (n < npix_min || n < 1) return false;                                              // uniform
     const int B = sh[32], r = sh[33], M = sh[34];
     float lo = 0.f, hi = 0.f; bool have_lo = false, have_hi = false;
     if (B > 0 && B < LQ_NB - 1 && M <= CAP) {                                             // uniform, the usual case
-        lq_collect_rank<NT, NK, CAP, BP>(x, elig, b, B, r, M, sh, list, lo, hi, have_hi);
+        lq_collect_rank<NT, NK, CAP, BP>(x, elig, b, B, r, M, sh, list, lo, hi, have_hi, g);
         have_lo = true;
     }
     if (!have_lo || (!have_hi && (n & 1) == 0)) {                                         // uniform, rare
         float xs[NK], res[3];
 #pragma unroll
         for (int i = 0; i < NK; ++i) xs[i] = x[i];
-        lq_median_slow<NT, NK, CAP, BP>(xs, elig, n, have_lo, lo, b, hist, sh, list, redbuf, res);
+        lq_median_slow<NT, NK, CAP, BP>(xs, elig, n, have_lo, lo, b, hist, sh, list, redbuf, res, g);
         lo = res[0]; hi = res[1]; b = res[2];
     }
     if (n & 1) hi = lo;
@@ -1275,7 +1319,7 @@ cm_banks_epix_fi_kernel(const uint16_t* __restrict__ raw, float* __restrict__ ou
 
         // common_mode_2d: skip if n < npix_min, skip if |cm| > cormax.  An unapplied correction is cm = +0: x - 0 == x for every x.
         float lo, hi, cm = 0.f;
-        if (block_median_linear<NT, NK, CAP, BP>(x, elig, c.npix_min, bcen, hist, selsh, list, redbuf, lo, hi)) {      // uniform
+        if (block_median_linear<NT, NK, CAP, BP>(x, elig, c.npix_min, bcen, hist, selsh, list, redbuf, lo, hi, CtaGroup{})) {      // uniform
             const float med = psr_mid(lo, hi);
             if (!(fabsf(med) > c.cormax)) cm = med;
         }
@@ -1335,6 +1379,10 @@ cm_banks_epix_pair_kernel(const uint16_t* __restrict__ raw, float* __restrict__ 
     extern __shared__ float4 sm4[];                               // [4][NCH]: ped0, ped1, gf0, gf1 of the 4 pixels of a chunk
     int* sgp = reinterpret_cast<int*>(sm4 + 4 * NCH);             // [CPT][NT] first pixel of a thread's chunk; IMG: + [CPT][NT] its image index
     uint2* sraw = reinterpret_cast<uint2*>(sgp + 2 * CPT * NT);   // [NF][CPT][NT] the next pair's raw chunks, staged by cp.async (each thread its own)
+    // the second frame's values wait here between the phases (each thread its own slots) instead of in 12 more registers,
+    // which ptxas would spill to local memory one by one
+    float4* park = reinterpret_cast<float4*>(sraw + (PSR_PAIR_STAGE ? NF * CPT * NT : 0));      // [CPT][NT]
+    constexpr bool PARK = PSR_PAIR_PARK && NF == 2;
     __shared__ int redbuf[64];
     __shared__ __align__(16) uint32_t hist[NF][LQ_NB];
     __shared__ __align__(16) float list[NF][CAP + 4];
@@ -1466,6 +1514,10 @@ cm_banks_epix_pair_kernel(const uint16_t* __restrict__ raw, float* __restrict__ 
                 const uint32_t m = (elig[f] << (31 - BP::pos(i))) >> 31;                              // ineligible: add 0 (no branch around the atomic)
                 asm volatile("red.shared.add.u32 [%0], %1;" :: "r"(ad), "r"(m) : "memory");
             }
+            if (PARK && f == 1) {
+#pragma unroll
+                for (int j = 0; j < CPT; ++j) park[j * NT + tid] = make_float4(x[1][j * 4], x[1][j * 4 + 1], x[1][j * 4 + 2], x[1][j * 4 + 3]);
+            }
         }
         __syncthreads();
         // scans: warps 0-7 take frame 0's bins, warps 8-15 frame 1's
@@ -1512,6 +1564,10 @@ cm_banks_epix_pair_kernel(const uint16_t* __restrict__ raw, float* __restrict__ 
                 uint32_t hits = 0; float cand = 0.f;
                 float bb = bcen[f];
                 asm volatile("" : "+f"(bb));                      // the bins are recomputed, not kept from the histogram pass (12 registers)
+                if (PARK && f == 1) {
+#pragma unroll
+                    for (int j = 0; j < CPT; ++j) { const float4 v = park[j * NT + tid]; x[1][j * 4] = v.x; x[1][j * 4 + 1] = v.y; x[1][j * 4 + 2] = v.z; x[1][j * 4 + 3] = v.w; }
+                }
 #pragma unroll
                 for (int i = 0; i < NK; ++i)
                     if (lq_bits(x[f][i], LQ_A, bb) == target) { hits |= 1u << BP::pos(i); cand = x[f][i]; }
@@ -1559,8 +1615,8 @@ cm_banks_epix_pair_kernel(const uint16_t* __restrict__ raw, float* __restrict__ 
                 if (!fast[f] || (!have_hi && (nn[f] & 1) == 0)) { // uniform, rare: everything unusual, on a copy in local memory
                     float xs[NK], res[3];
 #pragma unroll
-                    for (int i = 0; i < NK; ++i) xs[i] = x[f][i];
-                    lq_median_slow<NT, NK, CAP, BP>(xs, elig[f], nn[f], fast[f], lo, bcen[f], &hist[f][0], &selsh[f][0], &list[f][0], redbuf, res);
+                    for (int i = 0; i < NK; ++i) xs[i] = (PARK && f == 1) ? reinterpret_cast<const float*>(&park[(i >> 2) * NT + tid])[i & 3] : x[f][i];
+                    lq_median_slow<NT, NK, CAP, BP>(xs, elig[f], nn[f], fast[f], lo, bcen[f], &hist[f][0], &selsh[f][0], &list[f][0], redbuf, res, CtaGroup{});
                     lo = res[0]; hi = res[1];
                 }
                 if (nn[f] & 1) hi = lo;
@@ -1576,16 +1632,20 @@ cm_banks_epix_pair_kernel(const uint16_t* __restrict__ raw, float* __restrict__ 
         for (int f = 0; f < NF; ++f) {
             if (f == 1 && !pair) break;
             float* outf = out + (size_t)(frame + f) * fout;
+            asm volatile("" : "+r"(elig[f]), "+r"(sbits[f]));     // single-bit tests are made here, not carried (spilled) from the load phase
 #pragma unroll
             for (int j = 0; j < CPT; ++j) {
                 const int ch = tid + j * NT;
                 const float4 ga = sm4[2 * NCH + ch], gb = sm4[3 * NCH + ch];
                 const float g0[4] = {ga.x, ga.y, ga.z, ga.w}, g1[4] = {gb.x, gb.y, gb.z, gb.w};
                 float o[8];
+                float xj[4];
+                if (PARK && f == 1) { const float4 v = park[j * NT + tid]; xj[0] = v.x; xj[1] = v.y; xj[2] = v.z; xj[3] = v.w; }
+                else { xj[0] = x[f][j * 4]; xj[1] = x[f][j * 4 + 1]; xj[2] = x[f][j * 4 + 2]; xj[3] = x[f][j * 4 + 3]; }
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     const int q = BP::pos(j * 4 + i);
-                    const float xv = psr_sub_if(x[f][j * 4 + i], cm[f], elig[f] & (1u << q));
+                    const float xv = psr_sub_if(xj[i], cm[f], elig[f] & (1u << q));
                     o[i] = psr_mul_sel(xv, g0[i], g1[i], sbits[f] & (1u << q));
                 }
                 if (use_keep) {
@@ -1596,6 +1656,158 @@ cm_banks_epix_pair_kernel(const uint16_t* __restrict__ raw, float* __restrict__ 
                 if constexpr (IMG) img_store_chunk<4>(outf, c.fwd + gp, (kinds >> (2 * j)) & 3u, sgp[(CPT + j) * NT + tid], o);
                 else __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
             }
+        }
+    }
+}
+
+// =================================================================================================
+// epix10ka, mode 4, TWO FRAME GROUPS: as the frame-pair kernel (one 704-thread CTA per SM, all of the bank
+// tile's constants staged once in shared memory), but the CTA is two groups of 352 threads that each take
+// every other frame of the CTA's share and synchronise only among themselves (hardware barriers 1 and 2):
+// the groups drift apart and fill each other's barrier and latency gaps, like two CTAs that share their
+// 135 KB of constants.  A thread holds 24 pixels (six 4-pixel chunks) of its group's frame.
+// =================================================================================================
+template <bool IMG>
+__global__ void __launch_bounds__(704, 1)
+cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c, int nframes, int fpc)
+{
+    constexpr int NT = 704, NG = 2, GT = NT / NG, ROWS = 352, COLS = 384, NB = 8, TR = ROWS / 2, TC = COLS / NB, CH = TC / 4, NCH = TR * CH;
+    constexpr int CPT = NCH / GT, NK = CPT * 4, CAP = GT;
+    using BP = BitsEpixWords4;
+    static_assert(NCH % NT == 0 && NCH % GT == 0 && CPT == 6, "tile layout");
+    extern __shared__ float4 sm4[];                               // [4][NCH]: ped0, ped1, gf0, gf1 of the 4 pixels of a chunk
+    int* sgp = reinterpret_cast<int*>(sm4 + 4 * NCH);             // [CPT][GT] first pixel of a thread's chunk; IMG: + [CPT][GT] its image index
+    __shared__ int redbuf[NG][64];
+    __shared__ __align__(16) uint32_t hist[NG][LQ_NB];
+    __shared__ __align__(16) float list[NG][CAP + 4];
+    __shared__ __align__(16) int selsh[NG][48];
+
+    const int tid = threadIdx.x, grp = tid / GT, t = tid - grp * GT;
+    int bid = blockIdx.x;
+    const int bank = bid % NB; bid /= NB;
+    const int half = bid & 1;  bid >>= 1;
+    const int seg = bid;
+    const int f_begin = blockIdx.y * fpc, f_end = min(nframes, f_begin + fpc);
+    const int tile0 = ((seg * ROWS + half * TR) * COLS) + bank * TC;
+
+    for (int i = tid; i < NG * LQ_NB; i += NT) (&hist[0][0])[i] = 0u;
+    // the tile's constants, by all 704 threads; the mask is folded into the gain factors (psr_set_constants)
+#pragma unroll
+    for (int j = 0; j < NCH / NT; ++j) {
+        const int ch = tid + j * NT;
+        const int r = ch / CH, cc = ch - r * CH;
+        const int gp = tile0 + r * COLS + cc * 4;
+        sm4[0 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped0 + gp));
+        sm4[1 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped1 + gp));
+        sm4[2 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.gf0 + gp));
+        sm4[3 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.gf1 + gp));
+    }
+    uint32_t kbits = 0, e0bits = 0, e1bits = 0;                   // bit BP::pos(i) = value i of this thread
+    uint32_t kinds = 0;                                           // IMG: where each chunk goes in the assembled image is the same for every frame
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+        const int ch = t + j * GT;
+        const int r = ch / CH, cc = ch - r * CH;
+        const int gp = tile0 + r * COLS + cc * 4;
+        if (grp == 0) sgp[j * GT + t] = gp;
+        const uint32_t f = __ldg(reinterpret_cast<const uint32_t*>(c.flags + gp));
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t fb = (f >> (8 * i)) & 0xFFu;
+            const int q = BP::pos(j * 4 + i);
+            kbits |= ((fb & PSR_FL_KEEP) ? 1u : 0u) << q;
+            e0bits |= ((fb & PSR_FL_ELIG0) ? 1u : 0u) << q;
+            e1bits |= ((fb & PSR_FL_ELIG1) ? 1u : 0u) << q;
+        }
+        if constexpr (IMG) {
+            int t0; kinds |= img_chunk_kind<4>(c.fwd + gp, t0) << (2 * j);
+            if (grp == 0) sgp[(CPT + j) * GT + t] = t0;
+        }
+    }
+    const bool use_keep = c.has_keep && !c.ignore_keep;           // uniform: np.where(keep, v, 0) only when a keep mask is installed
+    const size_t fout = IMG ? (size_t)c.H * c.W : (size_t)c.npix;
+    // always 0 (this kernel is epix10ka's), but not to the compiler: lets a value be made to depend on another, which
+    // keeps ptxas from hoisting every chunk's loads to the top and spilling the values it has already computed
+    const uint32_t zero = (uint32_t)c.det_kind;
+    __syncthreads();
+
+    const WarpGroup<GT> g{t, 1 + grp};
+    float bcen = 0.5f;                                            // histogram window centred on 0, then on the group's previous median
+    for (int frame = f_begin + grp; frame < f_end; frame += NG) {
+        const uint16_t* rawf = raw + (size_t)frame * c.npix;
+        float* outf = out + (size_t)frame * fout;
+        float x[NK];
+        uint32_t sbits = 0;                                       // bit BP::pos(i) = data bit 14 of value i
+        asm volatile("" : "+r"(kbits));                           // not loop-invariant to the compiler: it would hoist (and spill) the single-bit tests
+        uint2 rv[CPT];
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) rv[j] = __ldcs(reinterpret_cast<const uint2*>(rawf + sgp[j * GT + t]));
+        if (frame + NG < f_end) {                                 // the group's next raw tile on its way into L2 meanwhile
+#pragma unroll
+            for (int j = 0; j < CPT; ++j) asm volatile("prefetch.global.L2 [%0];" :: "l"(rawf + (size_t)NG * c.npix + sgp[j * GT + t]));
+        }
+        uint32_t chain = 0;
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+            const int ch = t + j * GT + (int)chain;               // chunk j's pedestals are fetched once chunk j - 1 is done
+            const uint32_t w[2] = {rv[j].x, rv[j].y};
+            const float4 p0 = sm4[0 * NCH + ch], p1 = sm4[1 * NCH + ch];
+            const float pa[4] = {p0.x, p0.y, p0.z, p0.w}, pb[4] = {p1.x, p1.y, p1.z, p1.w};
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                // both bit-14 flags of the word with one shift: bit 14 -> 2j + k, bit 30 -> 16 + 2j + k
+                sbits |= (w[k] >> (14 - 2 * j - k)) & (0x00010001u << (2 * j + k));
+#if PSR_CMF_MAGIC
+                const uint32_t wm = w[k] & 0x3FFF3FFFu;
+                // float(v) without a conversion: 0x4B000000 | v is 2^23 + v; both subtractions are exact or correctly rounded
+                const float fe = __fsub_rn(__uint_as_float(__byte_perm(wm, 0x4B000000u, 0x7610)), 8388608.0f);
+                const float fo = __fsub_rn(__uint_as_float(__byte_perm(wm, 0x4B000000u, 0x7632)), 8388608.0f);
+#else
+                const float fe = (float)(w[k] & 0x3FFFu), fo = (float)((w[k] >> 16) & 0x3FFFu);
+#endif
+                x[j * 4 + 2 * k] = psr_sub_sel(fe, pa[2 * k], pb[2 * k], w[k] & 0x4000u);
+                x[j * 4 + 2 * k + 1] = psr_sub_sel(fo, pa[2 * k + 1], pb[2 * k + 1], w[k] & 0x40000000u);
+            }
+#if PSR_CMF_CHAIN
+            chain = __float_as_uint(x[j * 4 + 3]) & zero;
+#endif
+        }
+        const uint32_t elig = (sbits & e1bits) | (~sbits & e0bits);
+
+        // common_mode_2d: skip if n < npix_min, skip if |cm| > cormax.  An unapplied correction is cm = +0: x - 0 == x for every x.
+        float lo, hi, cm = 0.f;
+        if (block_median_linear<GT, NK, CAP, BP>(x, elig, c.npix_min, bcen, &hist[grp][0], &selsh[grp][0], &list[grp][0], &redbuf[grp][0], lo, hi, g)) {
+            const float med = psr_mid(lo, hi);
+            if (!(fabsf(med) > c.cormax)) cm = med;
+        }
+
+        chain = 0;
+        uint32_t eligq = elig, sbitsq = sbits;
+#if PSR_CMF_OPAQUE
+        asm volatile("" : "+r"(eligq), "+r"(sbitsq));             // single-bit tests are made here, not carried (spilled) from the load phase
+#endif
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+            const int ch = t + j * GT + (int)chain;               // one chunk's gain factors in registers at a time
+            const float4 ga = sm4[2 * NCH + ch], gb = sm4[3 * NCH + ch];
+            const float g0[4] = {ga.x, ga.y, ga.z, ga.w}, g1[4] = {gb.x, gb.y, gb.z, gb.w};
+            float o[8];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int q = BP::pos(j * 4 + i);
+                const float xv = psr_sub_if(x[j * 4 + i], cm, eligq & (1u << q));
+                o[i] = psr_mul_sel(xv, g0[i], g1[i], sbitsq & (1u << q));
+            }
+            if (use_keep) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) if (!(kbits & (1u << BP::pos(j * 4 + i)))) o[i] = 0.0f;
+            }
+#if PSR_CMF_CHAIN
+            chain = __float_as_uint(o[3]) & zero;
+#endif
+            const int gp = sgp[j * GT + t];
+            if constexpr (IMG) img_store_chunk<4>(outf, c.fwd + gp, (kinds >> (2 * j)) & 3u, sgp[(CPT + j) * GT + t], o);
+            else __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
         }
     }
 }
@@ -1622,10 +1834,14 @@ constexpr size_t EPIX_FI_SMEM = (size_t)1056 * (4 * 16) + (size_t)6 * 352 * 4;  
 #ifndef PSR_CM_PAIR
 #define PSR_CM_PAIR 1          /* epix10ka bank medians: 1 = frame-pair kernel (704 threads, all constants in shared memory) */
 #endif
+#ifndef PSR_CM_GROUPS
+#define PSR_CM_GROUPS 1        /* epix10ka bank medians: 1 = two-frame-group kernel instead of the frame-pair kernel */
+#endif
+constexpr size_t EPIX_GROUPS_SMEM = (size_t)2112 * (4 * 16) + (size_t)12 * 352 * 4;   // all four constant tables of one bank tile + per-thread chunk offsets
 #ifndef PSR_CM_PAIR_FPC
 #define PSR_CM_PAIR_FPC 16     /* frames per CTA of the frame-pair kernel */
 #endif
-constexpr size_t EPIX_PAIR_SMEM = (size_t)2112 * (4 * 16) + (size_t)6 * 704 * 4 + (PSR_PAIR_STAGE ? (size_t)2 * 3 * 704 * 8 : 0);   // all four constant tables of one bank tile + per-thread chunk offsets + a pair of raw tiles
+constexpr size_t EPIX_PAIR_SMEM = (size_t)2112 * (4 * 16) + (size_t)6 * 704 * 4 + (PSR_PAIR_STAGE ? (size_t)2 * 3 * 704 * 8 : 0) + (PSR_PAIR_PARK ? (size_t)3 * 704 * 16 : 0);   // all four constant tables of one bank tile + per-thread chunk offsets + a pair of raw tiles
 
 }  // namespace
 
@@ -1640,6 +1856,10 @@ cudaError_t psr_common_mode_setup(void)
         e = cudaFuncSetAttribute(cm_banks_kernel<1, 512, 1024, 16, PSR_CMB_JF_NT, PSR_CMB_JF_MINB, PSR_CMB_JF_CW, PSR_CMB_JF_KS != 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * 64 * 4);
         if (e != cudaSuccess) return e;
     }
+    e = cudaFuncSetAttribute(cm_banks_epix_groups_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_GROUPS_SMEM);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(cm_banks_epix_groups_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_GROUPS_SMEM);
+    if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(cm_banks_epix_pair_kernel<false, PSR_PAIR_NF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_PAIR_SMEM);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(cm_banks_epix_pair_kernel<true, PSR_PAIR_NF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_PAIR_SMEM);
@@ -1660,7 +1880,8 @@ cudaError_t launch_banks(const PsrDev& c, const uint16_t* d_raw, int nframes, fl
         if (PSR_CM_PAIR && nframes > 1) {
             const int fpc = PSR_CM_PAIR_FPC;
             dim3 g2((unsigned)c.nseg * 2 * 8, (unsigned)((nframes + fpc - 1) / fpc));
-            cm_banks_epix_pair_kernel<IMG, PSR_PAIR_NF><<<g2, 704, EPIX_PAIR_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
+            if (PSR_CM_GROUPS) cm_banks_epix_groups_kernel<IMG><<<g2, 704, EPIX_GROUPS_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
+            else cm_banks_epix_pair_kernel<IMG, PSR_PAIR_NF><<<g2, 704, EPIX_PAIR_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
         } else if (PSR_CM_FPC > 1 && nframes > 1) {
             const int fpc = PSR_CM_FPC;
             dim3 g2((unsigned)c.nseg * 2 * 8, (unsigned)((nframes + fpc - 1) / fpc));
