@@ -1,14 +1,17 @@
 #!/usr/bin/env python
 """bench.py -- calibrated frames/s of the psana-ray hot path on B200.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload calib|cm|image|jungfrau] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload calib|cm|image|image_nocm|jungfrau] [--impl ours|reference]
 
 A step is one pass of the hot path over one batch of synthetic raw frames (default workload =
 BASELINE.json configs[1]: epix10k2M pedestal + gain-switch calibration, batch 64, one B200).  Prints
 ONE JSON line: the device-resident throughput (`value`), the end-to-end number through the C ABI
-with host buffers (`e2e`), the roofline of the dominant kernel and the CPU baseline (NumPy oracle on
-this box's host cores).  For N > 1 launch with torch.distributed.run, one rank per GPU; events
-shard by rank, there is no data-path collective (weak scaling).
+from pinned host memory with the WHOLE calibrated batch copied back (`e2e`; the GPU-resident hand-off
+beside it as `e2e.device_resident_out`), the roofline of the step and the CPU baseline (NumPy oracle
+on this box's host cores).  The other BASELINE.json workloads (configs[2] with and without the
+image, configs[3] Jungfrau) are measured briefly in the same run into `workloads`, each with its own
+`value`, `roofline` and `e2e`.  For N > 1 launch with torch.distributed.run, one rank per GPU;
+events shard by rank, there is no data-path collective (weak scaling).
 """
 from __future__ import annotations
 
@@ -31,7 +34,7 @@ BATCH = 64
 METRIC = "calibrated epix10k2M frames/sec"
 WORKLOADS = {
     # name -> (detector, common-mode cmpars, image?, BASELINE.json config it is)
-    "calib":    ("epix10k2M", None, False, "configs[1]: epix10k2M pedestal + gain-switch calibration, batch 64, constants L2-resident"),
+    "calib":    ("epix10k2M", None, False, "configs[1]: epix10k2M pedestal + gain-switch calibration, batch 64, constants on-chip across the batch"),
     "cm":       ("epix10k2M", (7, 4, 100.0, 10), False, "configs[2] (calib part): epix10k2M calib + per-bank common-mode median + mask, batch 64"),
     "image":    ("epix10k2M", (7, 4, 100.0, 10), True, "configs[2]: epix10k2M calib + per-bank common-mode median + mask + assembled image, batch 64"),
     "image_nocm": ("epix10k2M", None, True, "epix10k2M calib fused with image assembly, batch 64"),
@@ -217,6 +220,173 @@ def reference_arm(args, rank, world):
     return 0
 
 
+def tiled_raw(syn, spec, consts, B, seed):
+    """B raw frames: 16 distinct synthetic frames, tiled; the repeats get their lowest two ADC bits flipped so that every
+    frame differs while the noise statistics stay those of SURVEY.md 8d (the common-mode medians depend on them)."""
+    raw = syn.make_raw_frames(spec, consts, min(B, 16), seed=seed)
+    if raw.shape[0] < B:
+        reps = (B + raw.shape[0] - 1) // raw.shape[0]
+        raw = np.concatenate([raw] * reps)[:B].copy()
+        raw[16:] ^= (np.arange(B - 16, dtype=np.uint16) % 3 + 1)[:, None, None, None]
+    return raw
+
+
+def pcie_probe(torch, du, world, rank, nbytes=256 << 20, reps=8):
+    """This box's pinned-copy rates with every rank copying at once, H2D and D2H as SEPARATE barrier-bracketed phases
+    (a probe that mixes directions across drifting ranks is not a denominator).  Returns per-rank min / median and the
+    node aggregate, GB/s."""
+    h_buf = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    d_buf = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+
+    def phase(dst, src):
+        dst.copy_(src, non_blocking=True); torch.cuda.synchronize()
+        du.barrier(); torch.cuda.synchronize()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(reps):
+            dst.copy_(src, non_blocking=True)
+        a1.record(); torch.cuda.synchronize()
+        du.barrier()
+        return reps * nbytes / (a0.elapsed_time(a1) / 1e3) / 1e9
+
+    out = {}
+    for name, dst, src in (("h2d", d_buf, h_buf), ("d2h", h_buf, d_buf)):
+        mine = phase(dst, src)
+        allr = sorted(du.gather_floats(mine, device="cuda"))
+        out[name] = {"this_rank": mine, "per_rank_min": allr[0], "per_rank_median": allr[len(allr) // 2], "node_aggregate": sum(allr)}
+    out["how"] = f"{nbytes >> 20} MiB pinned cudaMemcpyAsync x {reps} per rank, all {world} ranks at once, one direction per barrier-bracketed phase, before the e2e loops"
+    del h_buf, d_buf
+    return out
+
+
+def measure(torch, du, syn, GpuCalibrator, name, B, steps, warmup, e2e_steps, dev, rank, world, frames_per_block=0,
+            sampler=None, pcie=None, wc_staging=False):
+    """One workload on this rank's GPU: device-resident throughput (CUDA events per step, max over ranks), the roofline
+    of its step, and the end-to-end numbers through the C ABI from pinned host memory."""
+    detector, cmpars, image, cfgname = WORKLOADS[name]
+    spec = syn.detector_spec(detector)
+    consts = syn.make_constants(spec, seed=0)
+    raw = tiled_raw(syn, spec, consts, B, seed=1000 + rank)
+    cal = GpuCalibrator(spec, device=dev)
+    cal.set_constants(consts["peds"], consts.get("gain"), consts.get("offs"), consts.get("cfg"), consts.get("mask"))
+    cal.set_common_mode(cmpars)
+    image_shape = None
+    if image:
+        image_shape = cal.set_geometry(*syn.make_pixel_index_arrays(spec))
+        cal.reserve(B)
+    if frames_per_block:
+        cal.set_option("frames_per_block", frames_per_block)
+
+    def barrier():
+        du.barrier()
+        torch.cuda.synchronize()
+
+    h_raw = torch.from_numpy(raw.view(np.int16)).pin_memory()
+    d_raw = h_raw.cuda(non_blocking=True)
+    d_out = torch.empty(cal.out_shape(B, image), dtype=torch.float32, device="cuda")
+    h_out = torch.empty(cal.out_shape(B, image), dtype=torch.float32).pin_memory()
+    stream = torch.cuda.current_stream()
+    launches_per_step = cal.launches_per_batch(B, image)
+
+    # ---- device-resident throughput ---------------------------------------------------------------
+    for _ in range(warmup):
+        cal.calib(d_raw, out=d_out, image=image)
+    barrier()
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    if sampler is not None:
+        sampler.start()
+    t_wall0 = time.perf_counter()
+    evs[0].record(stream)
+    for i in range(steps):
+        cal.calib(d_raw, out=d_out, image=image)
+        evs[i + 1].record(stream)
+    barrier()
+    t_wall1 = time.perf_counter()
+    total_ms = evs[0].elapsed_time(evs[-1])
+    step_ms = [evs[i].elapsed_time(evs[i + 1]) for i in range(steps)]
+    clocks = None
+    if sampler is not None:
+        if len([s for s in sampler.samples if t_wall0 <= s[0] <= t_wall1]) < 3:     # short region: probe the clocks under the same load
+            t_end = time.perf_counter() + 0.25
+            while time.perf_counter() < t_end:
+                for _ in range(20):
+                    cal.calib(d_raw, out=d_out, image=image)
+                torch.cuda.synchronize()
+        sampler.stop()
+        clocks = sampler.summary(t_wall0, t_wall1)
+    total_ms_max = du.max_over_ranks(total_ms, device="cuda")
+    value = du.whole_job_throughput(B * steps, world, total_ms_max / 1e3)
+
+    # ---- end to end through the C ABI from HOST buffers ---------------------------------------------------
+    def timed(fn, n):
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(n):
+            fn()
+        barrier()
+        # the calls block on the library's own streams, so the host clock brackets the device work
+        return du.whole_job_throughput(B * n, world, du.max_over_ranks(time.perf_counter() - t0, device="cuda"))
+
+    # (1) the headline: pinned host raw in, the WHOLE calibrated batch back in pinned host memory -- what the reference's
+    #     consumer gets from DataReader.read() (ref: data_reader.py:35 returns host arrays)
+    for _ in range(3):
+        cal.calib_host(h_raw, h_out=h_out, image=image)
+    e2e_host = timed(lambda: cal.calib_host(h_raw, h_out=h_out, image=image), e2e_steps)
+    # (2) the product's hand-off: the calibrated batch STAYS on the GPU (CUDA-IPC handle to the consumers); one calibrated
+    #     frame is read back as the step's result
+    h_frame = torch.empty(tuple(d_out.shape[1:]), dtype=torch.float32).pin_memory()
+
+    def resident_step():
+        cal.calib_host(h_raw, d_out=d_out, image=image)      # synchronous: returns when d_out is final
+        h_frame.copy_(d_out[B - 1], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    for _ in range(3):
+        resident_step()
+    e2e_resident = timed(resident_step, e2e_steps)
+
+    peak, peak_src = measured_peaks()
+    alg_bytes = algorithmic_bytes_per_frame(spec, image_shape) * B
+    avg_launch_s = (sum(step_ms) / len(step_ms)) / 1e3
+    achieved = alg_bytes / avg_launch_s / 1e9
+    h2d_bytes = raw.nbytes
+    d2h_bytes = h_out.numel() * 4
+    res = {
+        "metric": METRIC.replace("epix10k2M", detector), "value": value, "unit": "frames/s", "steps": steps,
+        "ms_per_step": total_ms_max / steps,
+        "config": {"workload": cfgname, "detector": spec.name, "frame_shape": list(spec.shape), "batch_per_gpu": B,
+                   "common_mode": list(cmpars) if cmpars else None, "image": image_shape,
+                   "sharding": "events by rank, no collective" if world > 1 else "single GPU",
+                   "l2": f"inputs larger than L2: {raw.nbytes / 1e6:.0f} MB raw in + {d_out.numel() * 4 / 1e6:.0f} MB out per step vs 126 MB L2",
+                   "seed": 1000},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": ncu_traffic(name), "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_ms": avg_launch_s * 1e3,
+                     "min_launch_ms": min(step_ms), "kernel_launches_per_step": launches_per_step},
+        "e2e": {"value": e2e_host, "unit": "frames/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
+                "steps": e2e_steps,
+                "path": "psr_calib_batch_host: pinned host raw -> H2D chunks on a side stream -> kernels -> D2H of every calibrated "
+                        "chunk on a third stream -> the whole calibrated batch in pinned host memory",
+                "pcie_frac_of_63GBs_d2h": e2e_host / world * (d2h_bytes / B) / 1e9 / 63.0,
+                "device_resident_out": {
+                    "value": e2e_resident, "unit": "frames/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": h_frame.numel() * 4,
+                    "path": "same H2D + kernels; the batch stays on the GPU for the CUDA-IPC hand-off, one calibrated frame read back",
+                    "pcie_frac_of_63GBs_h2d": e2e_resident / world * (h2d_bytes / B) / 1e9 / 63.0}},
+        "gpu_launches": steps * launches_per_step,
+    }
+    if pcie is not None:
+        res["e2e"]["pcie_measured_gbs"] = pcie
+        # against what THIS box gives with every rank copying at once (slowest rank = the job's pace)
+        res["e2e"]["frac_of_measured_d2h"] = e2e_host / world * (d2h_bytes / B) / 1e9 / pcie["d2h"]["per_rank_min"]
+        res["e2e"]["device_resident_out"]["frac_of_measured_h2d"] = e2e_resident / world * (h2d_bytes / B) / 1e9 / pcie["h2d"]["per_rank_min"]
+    if clocks is not None:
+        res["clocks"] = clocks
+    cal.close()
+    del d_raw, d_out, h_out, h_raw
+    torch.cuda.empty_cache()
+    return res
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -230,6 +400,9 @@ def main():
     ap.add_argument("--cpu-procs", type=int, default=0, help="CPU reference processes (0 = all host cores)")
     ap.add_argument("--cpu-frames-per-proc", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--also", default="jungfrau,cm,image,image_nocm",
+                    help="other BASELINE.json workloads measured into the line's `workloads` object (comma list, '' = none)")
+    ap.add_argument("--also-steps", type=int, default=10)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -267,145 +440,25 @@ def main():
     numa_cpus = du.bind_to_gpu_numa(dev)              # before any pinned allocation: staging memory next to the GPU
     du.init("nccl", device=torch.device("cuda", dev))
 
-    def barrier():
-        du.barrier()
-        torch.cuda.synchronize()
-
-    spec = syn.detector_spec(detector)
-    consts = syn.make_constants(spec, seed=0)
-    B = args.batch
-    raw = syn.make_raw_frames(spec, consts, min(B, 16), seed=1000 + rank)
-    if raw.shape[0] < B:      # tile 16 distinct frames and perturb the ADC bits so every frame differs
-        reps = (B + raw.shape[0] - 1) // raw.shape[0]
-        raw = np.concatenate([raw] * reps)[:B].copy()
-        raw[16:] ^= (np.arange(B - 16, dtype=np.uint16) * 37 % 512 + 1)[:, None, None, None]
-    cal = GpuCalibrator(spec, device=dev)
-    cal.set_constants(consts["peds"], consts.get("gain"), consts.get("offs"), consts.get("cfg"), consts.get("mask"))
-    cal.set_common_mode(cmpars)
-    image_shape = None
-    if image:
-        image_shape = cal.set_geometry(*syn.make_pixel_index_arrays(spec))
-        cal.reserve(B)
-    if args.frames_per_block:
-        cal.set_option("frames_per_block", args.frames_per_block)
-
-    h_raw = torch.from_numpy(raw.view(np.int16)).pin_memory()
-    d_raw = h_raw.cuda(non_blocking=True)
-    d_out = torch.empty(cal.out_shape(B, image), dtype=torch.float32, device="cuda")
-    h_out = torch.empty(cal.out_shape(B, image), dtype=torch.float32).pin_memory()
-    stream = torch.cuda.current_stream()
-    launches_per_step = 2 if image else 1           # image modes: the scatter / common-mode kernel + the gap-fill kernel beside it
-
-    # ---- device-resident throughput ---------------------------------------------------------------
-    sampler = ClockSampler(dev)
-    for _ in range(args.warmup):
-        cal.calib(d_raw, out=d_out, image=image)
-    barrier()
-    evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
-    sampler.start()
-    t_wall0 = time.perf_counter()
-    evs[0].record(stream)
-    for i in range(args.steps):
-        cal.calib(d_raw, out=d_out, image=image)
-        evs[i + 1].record(stream)
-    barrier()
-    t_wall1 = time.perf_counter()
-    total_ms = evs[0].elapsed_time(evs[-1])
-    step_ms = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
-    if len([s for s in sampler.samples if t_wall0 <= s[0] <= t_wall1]) < 3:     # short region: probe the clocks under the same load
-        t_end = time.perf_counter() + 0.25
-        while time.perf_counter() < t_end:
-            for _ in range(20):
-                cal.calib(d_raw, out=d_out, image=image)
-            torch.cuda.synchronize()
-    sampler.stop()
-    clocks = sampler.summary(t_wall0, t_wall1)
-    total_ms_max = du.max_over_ranks(total_ms, device="cuda")
-    value = du.whole_job_throughput(B * args.steps, world, total_ms_max / 1e3)
-
-    # ---- end to end through the C ABI from HOST buffers ---------------------------------------------------
-    # The product path (what the producer does per batch): pinned host raw -> H2D in chunks on a side stream ->
-    # kernels -> the calibrated batch STAYS on the GPU (it is handed to consumers by CUDA-IPC handle) -> one
-    # calibrated frame of the batch is read back to pinned host memory as the step's result.
+    pcie = pcie_probe(torch, du, world, rank)         # the box's real pinned-copy rates, before anything else loads the links
     e2e_steps = args.e2e_steps or min(args.steps, 20)
-    h_frame = torch.empty(tuple(d_out.shape[1:]), dtype=torch.float32).pin_memory()
-
-    def e2e_step():
-        cal.calib_host(h_raw, d_out=d_out, image=image)      # synchronous: returns when d_out is final
-        h_frame.copy_(d_out[B - 1], non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-
-    def timed(fn, n):
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(n):
-            fn()
-        barrier()
-        # the calls block on the library's own streams, so the host clock brackets the device work
-        return du.whole_job_throughput(B * n, world, du.max_over_ranks(time.perf_counter() - t0, device="cuda"))
-
-    for _ in range(3):
-        e2e_step()
-    e2e_value = timed(e2e_step, e2e_steps)
-    # the same with the whole calibrated batch copied back to pinned host memory (a host-side consumer)
-    for _ in range(2):
-        cal.calib_host(h_raw, h_out=h_out, image=image)
-    e2e_host_value = timed(lambda: cal.calib_host(h_raw, h_out=h_out, image=image), e2e_steps)
-
-    # ---- the box's real pinned-copy peaks (256 MB cudaMemcpyAsync loop), the PCIe denominators next to 63 GB/s ----
-    def copy_peak(dst, src, reps=8):
-        dst.copy_(src, non_blocking=True); torch.cuda.synchronize()
-        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a0.record()
-        for _ in range(reps):
-            dst.copy_(src, non_blocking=True)
-        a1.record(); torch.cuda.synchronize()
-        return reps * src.numel() * src.element_size() / (a0.elapsed_time(a1) / 1e3) / 1e9
-    nb = 256 << 20
-    h_buf = torch.empty(nb, dtype=torch.uint8).pin_memory()
-    d_buf = torch.empty(nb, dtype=torch.uint8, device="cuda")
-    barrier()
-    h2d_peak = copy_peak(d_buf, h_buf)
-    d2h_peak = copy_peak(h_buf, d_buf)
-    del h_buf, d_buf
-
-    # ---- roofline of the dominant kernel (one launch = one step's batch) ------------------------------
-    peak, peak_src = measured_peaks()
-    alg_bytes = algorithmic_bytes_per_frame(spec, image_shape) * B
-    avg_launch_s = (sum(step_ms) / len(step_ms)) / 1e3
-    achieved = alg_bytes / avg_launch_s / 1e9
-    pcie_peak = 63.0
-    h2d_bytes = raw.nbytes
-    d2h_bytes = h_out.numel() * 4
+    main_res = measure(torch, du, syn, GpuCalibrator, args.workload, args.batch, args.steps, args.warmup, e2e_steps, dev, rank, world,
+                       frames_per_block=args.frames_per_block, sampler=ClockSampler(dev), pcie=pcie)
+    others = {}
+    for name in [w for w in args.also.split(",") if w and w != args.workload]:
+        r = measure(torch, du, syn, GpuCalibrator, name, args.batch, args.also_steps, 3, min(args.also_steps, 5), dev, rank, world, pcie=pcie)
+        others[name] = {k: r[k] for k in ("metric", "value", "unit", "steps", "ms_per_step", "config", "roofline", "e2e", "gpu_launches")}
 
     if rank == 0:
         line = {
-            "metric": METRIC.replace("epix10k2M", detector), "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": total_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "metric": main_res["metric"], "value": main_res["value"], "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": main_res["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": cfgname, "detector": spec.name, "frame_shape": list(spec.shape), "batch_per_gpu": B,
-                       "common_mode": list(cmpars) if cmpars else None, "image": image_shape,
-                       "sharding": "events by rank, no collective" if world > 1 else "single GPU",
-                       "l2": f"inputs larger than L2: {raw.nbytes / 1e6:.0f} MB raw in + {d_out.numel() * 4 / 1e6:.0f} MB out per step vs 126 MB L2",
-                       "seed": 1000},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": ncu_traffic(args.workload), "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_ms": avg_launch_s * 1e3,
-                         "min_launch_ms": min(step_ms), "kernel_launches_per_step": launches_per_step},
-            "cpu_baseline": cpu_baseline,
-            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": h_frame.numel() * 4,
-                    "steps": e2e_steps,
-                    "path": "psr_calib_batch_host: pinned host raw -> H2D chunks on a side stream -> kernels -> batch resident on the GPU "
-                            "(CUDA-IPC hand-off) -> D2H of one calibrated frame as the step's result",
-                    "pcie_frac_of_63GBs_h2d": e2e_value / world * (h2d_bytes / B) / 1e9 / pcie_peak,
-                    "pcie_measured_gbs": {"h2d": h2d_peak, "d2h": d2h_peak, "how": "256 MiB pinned cudaMemcpyAsync x 8, this rank, all ranks copying at once"},
-                    "frac_of_measured_h2d": e2e_value / world * (h2d_bytes / B) / 1e9 / h2d_peak,
-                    "host_out": {"value": e2e_host_value, "unit": "frames/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
-                                 "pcie_frac_of_63GBs_d2h": e2e_host_value / world * (d2h_bytes / B) / 1e9 / pcie_peak,
-                                 "note": "whole calibrated batch copied back to pinned host memory, for a host-side consumer"}},
+            "config": main_res["config"], "roofline": main_res["roofline"], "cpu_baseline": cpu_baseline, "e2e": main_res["e2e"],
+            "workloads": others,
             "numa_bind_cpus": (f"{numa_cpus[0]}-{numa_cpus[-1]} ({len(numa_cpus)})" if numa_cpus else None),
-            "gpu_launches": args.steps * launches_per_step,
-            "clocks": clocks,
+            "gpu_launches": main_res["gpu_launches"],
+            "clocks": main_res.get("clocks"),
         }
         _emit(line)
     du.finalize()

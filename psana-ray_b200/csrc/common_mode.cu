@@ -47,18 +47,6 @@
 #ifndef PSR_LQ_ATOM             /* histogram update: 1 = unconditional add of 0/1, 0 = increment under a branch */
 #define PSR_LQ_ATOM 1
 #endif
-#ifndef PSR_PAIR_NF              /* frame-pair kernel: frames per pass (2, or 1 for comparison) */
-#define PSR_PAIR_NF 2
-#endif
-#ifndef PSR_PAIR_PARK            /* frame-pair kernel: the second frame's values wait in shared memory between the phases */
-#define PSR_PAIR_PARK 1
-#endif
-#ifndef PSR_PAIR_STAGE           /* frame-pair kernel: next pair's raw tiles staged in shared memory by cp.async */
-#define PSR_PAIR_STAGE 0
-#endif
-#ifndef PSR_PAIR_PREFETCH        /* frame-pair kernel: next pair's raw tiles prefetched into L2 */
-#define PSR_PAIR_PREFETCH 1
-#endif
 #ifndef PSR_CMF_OPAQUE
 #define PSR_CMF_OPAQUE 1
 #endif
@@ -67,9 +55,6 @@
 #endif
 #ifndef PSR_CM_UMULHI
 #define PSR_CM_UMULHI 0
-#endif
-#ifndef PSR_CM_BALLOT
-#define PSR_CM_BALLOT 0
 #endif
 
 namespace {
@@ -284,12 +269,12 @@ __device__ __forceinline__ uint32_t warp_kth_linear(const uint32_t (&key)[NK], i
     return pre;
 }
 
-// Keys of one thread parked in shared memory instead of registers: slot i of thread t at base[i * NT + t]
+// Values of one thread parked in shared memory instead of registers: slot i of thread t at base[i * NT + t]
 // (conflict-free), same [] syntax as a register array so the selection code serves both.
 template <int NT>
-struct SmemKeys {
-    uint32_t* base;                      // already offset by threadIdx.x
-    __device__ __forceinline__ uint32_t operator[](int i) const { return base[i * NT]; }
+struct SmemVals {
+    const float* base;                   // already offset by threadIdx.x
+    __device__ __forceinline__ float operator[](int i) const { return base[i * NT]; }
 };
 
 // ---- CTA-wide exact selection: 3-pass radix select (11 + 11 + 10 bits) on a 2048-bin shared histogram.
@@ -365,129 +350,6 @@ __device__ __forceinline__ uint32_t block_kth(const K& key, uint32_t elig, int k
 }
 
 
-// ---- median of the CTA's eligible keys, fast path --------------------------------------------------
-// Pass 0 histograms all keys on their top 11 bits.  The bin holding the median usually holds a few
-// hundred keys; those are compacted into a shared list and only the list is refined: one more
-// 11-bit pass over the list, then the (typically < 32) survivors are ranked by one warp, which yields
-// both middle order statistics at once.  Anything unusual (list overflow, many survivors, the upper
-// middle value outside the survivors) falls back to the register passes -- same exact answer.
-constexpr int LISTCAP = 1024;
-
-template <int NT, int NK, int NW, typename K>
-__device__ __forceinline__ void block_median_keys(const K& key, uint32_t elig, int n, uint32_t* hist, int* sh,
-                                                  uint32_t* list, BlockRed<NW>& red, uint32_t& lo_out, uint32_t& hi_out)
-{
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int k1 = (n - 1) >> 1, k2 = n >> 1;
-    for (int i = tid; i < 2048; i += NT) hist[i] = 0u;
-    if (tid == 0) { sh[35] = 0; sh[36] = 0; }
-    __syncthreads();
-    uint32_t prefix = 0; int k = k1;
-    block_kth_pass<NT, NK, 0>(key, elig, prefix, k, hist, sh);
-    const int M = sh[34];
-    bool have_lo = false, have_hi = false;
-    uint32_t lo = 0, hi = 0;
-    if (M <= LISTCAP) {                                         // uniform
-#if PSR_CM_BALLOT
-        // warp-aggregated append: one shared atomic per warp per step instead of one per matching key
-#pragma unroll
-        for (int i = 0; i < NK; ++i) {
-            const bool hit = ((elig >> i) & 1u) && (key[i] >> 21) == prefix;
-            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, hit);
-            if (bal) {
-                int base = 0;
-                if (lane == 0) base = atomicAdd(&sh[35], __popc(bal));
-                base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                if (hit) list[base + __popc(bal & ((1u << lane) - 1u))] = key[i];
-            }
-        }
-#else
-#pragma unroll
-        for (int i = 0; i < NK; ++i)
-            if (((elig >> i) & 1u) && (key[i] >> 21) == prefix) list[atomicAdd(&sh[35], 1)] = key[i];
-#endif
-        __syncthreads();
-        // pass 1 over the list: bits 20..10
-        const uint32_t haddr = (uint32_t)__cvta_generic_to_shared(hist);
-        for (int i = tid; i < M; i += NT)
-            asm volatile("red.shared.add.u32 [%0], 1;" :: "r"(haddr + (((list[i] >> 10) & 0x7FFu) << 2)) : "memory");
-        __syncthreads();
-        {   // find the bin of rank k among the list (same scan as block_kth_pass, keys come from the list)
-            constexpr int NB = 2048, BPT = (NB + NT - 1) / NT;
-            uint32_t b[BPT]; uint32_t s = 0;
-#pragma unroll
-            for (int j = 0; j < BPT; ++j) { const int idx = tid * BPT + j; b[j] = idx < NB ? hist[idx] : 0u; if (idx < NB) hist[idx] = 0u; s += b[j]; }
-            uint32_t incl = s;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
-            if (lane == 31) sh[warp] = (int)incl;
-            __syncthreads();
-            uint32_t base = 0;
-#pragma unroll
-            for (int w = 0; w < NW; ++w) base += (w < warp) ? (uint32_t)sh[w] : 0u;
-            const uint32_t excl = base + incl - s;
-            if ((uint32_t)k >= excl && (uint32_t)k < excl + s) {
-                uint32_t r = (uint32_t)k - excl; bool done = false;
-#pragma unroll
-                for (int j = 0; j < BPT; ++j)
-                    if (!done) { if (r < b[j]) { sh[32] = tid * BPT + j; sh[34] = (int)b[j]; done = true; } else r -= b[j]; }
-                sh[33] = (int)r;
-            }
-            __syncthreads();
-        }
-        const uint32_t prefix2 = (prefix << 11) | (uint32_t)sh[32];
-        const int r1 = sh[33], M1 = sh[34];
-        if (M1 <= 32) {                                         // uniform: survivors ranked by warp 0
-            uint32_t* list2 = list + LISTCAP;
-            for (int i = tid; i < M; i += NT)
-                if ((list[i] >> 10) == prefix2) list2[atomicAdd(&sh[36], 1)] = list[i];
-            __syncthreads();
-            if (warp == 0) {
-                const uint32_t v = lane < M1 ? list2[lane] : 0xFFFFFFFFu;
-                int rank = 0;
-                for (int j = 0; j < M1; ++j) {
-                    const uint32_t o = __shfl_sync(0xFFFFFFFFu, v, j);
-                    rank += (o < v) || (o == v && j < lane);
-                }
-                if (lane < M1 && rank == r1) sh[37] = (int)v;
-                if (lane < M1 && rank == r1 + 1) sh[38] = (int)v;
-            }
-            __syncthreads();
-            lo = (uint32_t)sh[37]; have_lo = true;
-            if (k2 == k1) { hi = lo; have_hi = true; }
-            else if (r1 + 1 < M1) { hi = (uint32_t)sh[38]; have_hi = true; }
-        } else {
-            prefix = prefix2; k = r1;                           // continue with the last register pass
-            uint32_t pfx = prefix2; int kk = r1;
-            block_kth_pass<NT, NK, 2>(key, elig, pfx, kk, hist, sh);
-            lo = pfx; have_lo = true;
-        }
-    } else {
-        block_kth_pass<NT, NK, 1>(key, elig, prefix, k, hist, sh);
-        block_kth_pass<NT, NK, 2>(key, elig, prefix, k, hist, sh);
-        lo = prefix; have_lo = true;
-    }
-    (void)have_lo;
-    if (!have_hi) {
-        hi = lo;
-        if (k2 != k1) {
-            int cle = 0; uint32_t mg = 0xFFFFFFFFu;
-#pragma unroll
-            for (int i = 0; i < NK; ++i)
-                if ((elig >> i) & 1u) { cle += (key[i] <= lo); if (key[i] > lo) mg = min(mg, key[i]); }
-            cle = red.sum(cle);
-            mg = red.minu(mg);
-            if (cle <= k2) hi = mg;
-        }
-    }
-    lo_out = lo; hi_out = hi;
-}
-
-// 8 bytes global -> shared, asynchronously, past L1
-__device__ __forceinline__ void psr_cp_async8(void* smem_dst, const void* gsrc) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
-}
-
 // Selects written as a predicated second operation: the arithmetic runs on the FMA pipe, which has room, instead
 // of a select on the ALU pipe, which is the one these kernels fill.  Same roundings as select-then-operate.
 __device__ __forceinline__ float psr_sub_sel(float f, float pa, float pb, uint32_t pick_b) {        // f - (pick_b ? pb : pa)
@@ -542,6 +404,8 @@ struct BitsLinear { static __device__ __forceinline__ constexpr int pos(int i) {
 // value i = pixel (2k + h) of chunk j (i = 8j + 2k + h: word k of the chunk's four raw words, low / high half):
 // bit 4j + k + 16h, the place where ONE shift of the raw word drops its two bit-14 flags
 struct BitsEpixWords { static __device__ __forceinline__ constexpr int pos(int i) { return 4 * (i >> 3) + ((i & 7) >> 1) + 16 * (i & 1); } };
+// the same for 4-pixel chunks (two raw words): value i = pixel (2k + h) of chunk j (i = 4j + 2k + h) -> bit 2j + k + 16h
+struct BitsEpixWords4 { static __device__ __forceinline__ constexpr int pos(int i) { return 2 * (i >> 2) + ((i & 3) >> 1) + 16 * (i & 1); } };
 
 // Who synchronises with whom: the whole CTA, or one of several equal groups of warps inside it, each on a hardware
 // barrier of its own (the groups then run their phases independently, like CTAs that share the tile's constants).
@@ -634,6 +498,8 @@ __device__ __forceinline__ void lq_pass(const X& x, uint32_t elig, float a, floa
                 if (!done) { if (rr < bn[j]) { sh[32] = 8 * tid + j; sh[33] = (int)rr; sh[34] = (int)bn[j]; done = true; } else rr -= bn[j]; }
         }
     }
+    if (tid == 0) sh[39] = (int)bn[0];                 // the two end bins: everything outside the window
+    if (tid == NSCAN - 1) sh[40] = (int)bn[7];
     if (tid == NT - 1) { sh[35] = 0; sh[36] = n; }
     g.sync();
 }
@@ -641,7 +507,7 @@ __device__ __forceinline__ void lq_pass(const X& x, uint32_t elig, float a, floa
 // The members of bin B (fine window b) are collected and ranked by one thread each: lo = rank r, hi = rank r + 1 when
 // the bin holds it (have_hi).  sh[35] must be 0 on entry (lq_pass leaves it so); M <= CAP.  Every thread must call it.
 template <int NT, int NK, int CAP, typename BP, typename X, typename G>
-__device__ __forceinline__ void lq_collect_rank(const X& x, uint32_t elig, float b, int B, int r, int M, int* sh, float* list,
+__device__ __forceinline__ void lq_collect_rank(const X& x, uint32_t elig, float a, float b, int B, int r, int M, int* sh, float* list,
                                                 float& lo, float& hi, bool& have_hi, const G& g)
 {
     static_assert(CAP <= NT && CAP % 4 == 0, "rank layout");
@@ -652,7 +518,7 @@ __device__ __forceinline__ void lq_collect_rank(const X& x, uint32_t elig, float
 #pragma unroll
     for (int i = 0; i < NK; ++i) {
         const float xi = x[i];
-        if (lq_bits(xi, LQ_A, b) == target) { hits |= 1u << BP::pos(i); cand = xi; }
+        if (lq_bits(xi, a, b) == target) { hits |= 1u << BP::pos(i); cand = xi; }
     }
     // a thread almost never holds two members of the bin: one candidate register, one branch per thread
     if (hits != 0u) {
@@ -690,7 +556,7 @@ __device__ __forceinline__ void lq_collect_rank(const X& x, uint32_t elig, float
 //   again.  What even that does not settle goes to a 32-step binary search on the float keys, one block-wide count per bit.
 // out[0] = lo, out[1] = hi, out[2] = the fine window's b as used (unchanged unless relocated).
 template <int NT, int NK, int CAP, typename BP, typename G>
-__device__ __noinline__ void lq_median_slow(const float* xs, uint32_t elig, int n, bool have_lo, float lo, float b,
+__device__ __noinline__ void lq_median_slow(const float* xs, uint32_t elig, int n, bool have_lo, float lo, float a, float b,
                                             uint32_t* hist, int* sh, float* list, int* redbuf, float* out, G g)
 {
     const LocalVals x{xs};
@@ -706,12 +572,12 @@ __device__ __noinline__ void lq_median_slow(const float* xs, uint32_t elig, int 
             g.sync();
             if (B > 0 && B < LQ_NB - 1) {
                 const float xc = __fmul_rn(__fsub_rn(__fmul_rn((float)B + 0.5f, 1.0f / (float)(LQ_NB - 1)), 0.5f), 1.0f / LQ_A_COARSE);
-                b = __fsub_rn(0.5f, __fmul_rn(xc, LQ_A));
-                lq_pass<NT, NK, BP>(x, elig, LQ_A, b, hist, sh, g);
+                b = __fsub_rn(0.5f, __fmul_rn(xc, a));
+                lq_pass<NT, NK, BP>(x, elig, a, b, hist, sh, g);
                 B = sh[32];
                 const int r = sh[33], M = sh[34];
                 if (B > 0 && B < LQ_NB - 1 && M <= CAP) {
-                    lq_collect_rank<NT, NK, CAP, BP>(x, elig, b, B, r, M, sh, list, lo, hi, have_hi, g);
+                    lq_collect_rank<NT, NK, CAP, BP>(x, elig, a, b, B, r, M, sh, list, lo, hi, have_hi, g);
                     have_lo = true;
                 }
             }
@@ -748,36 +614,47 @@ __device__ __noinline__ void lq_median_slow(const float* xs, uint32_t elig, int 
     out[0] = lo; out[1] = hi; out[2] = b;
 }
 
-// hist: LQ_NB words, all zero on entry and on exit; sh: 48 ints (16-byte aligned); list: CAP + 4 floats;
-// bcen: the window's b = 0.5 - centre / 64, updated to the median found.  Returns false (uniformly) when fewer than
+// hist: LQ_NB words, all zero on entry and on exit; sh: 48 ints (16-byte aligned); list: CAP + 4 floats.
+// win = the window carried from frame to frame: win.a = 1 / (window width in ADU), win.b = 0.5 - centre * a.  It is
+// re-centred on the median found and re-scaled to the distribution seen: twice as wide when more than an eighth of the
+// values fell outside it (they all hit the two end bins: atomics on one word, and a rank out there costs a relocation),
+// half as wide when the median's bin was crowded and the tails are empty.  Returns false (uniformly) when fewer than
 // max(npix_min, 1) values are eligible; else lo/hi = the two middle order statistics.  Every thread of the group must call it.
-template <int NT, int NK, int CAP, typename BP, typename G>
-__device__ __forceinline__ bool block_median_linear(const float (&x)[NK], uint32_t elig, int npix_min, float& bcen,
+struct LqWindow { float a, b; };
+constexpr float LQ_A_MIN = LQ_A_COARSE * 2.0f;
+
+template <int NT, int NK, int CAP, typename BP, typename X, typename G>
+__device__ __forceinline__ bool block_median_linear(const X& x, uint32_t elig, int npix_min, LqWindow& win,
                                                     uint32_t* hist, int* sh, float* list, int* redbuf,
                                                     float& lo_out, float& hi_out, const G& g)
 {
-    float b = bcen;
-    lq_pass<NT, NK, BP>(x, elig, LQ_A, b, hist, sh, g);
+    const float a = win.a;
+    float b = win.b;
+    lq_pass<NT, NK, BP>(x, elig, a, b, hist, sh, g);
     const int n = sh[36];
     if (n < npix_min || n < 1) return false;                                              // uniform
-    const int B = sh[32], r = sh[33], M = sh[34];
+    const int B = sh[32], r = sh[33], M = sh[34], tails = sh[39] + sh[40];
     float lo = 0.f, hi = 0.f; bool have_lo = false, have_hi = false;
     if (B > 0 && B < LQ_NB - 1 && M <= CAP) {                                             // uniform, the usual case
-        lq_collect_rank<NT, NK, CAP, BP>(x, elig, b, B, r, M, sh, list, lo, hi, have_hi, g);
+        lq_collect_rank<NT, NK, CAP, BP>(x, elig, a, b, B, r, M, sh, list, lo, hi, have_hi, g);
         have_lo = true;
     }
     if (!have_lo || (!have_hi && (n & 1) == 0)) {                                         // uniform, rare
         float xs[NK], res[3];
 #pragma unroll
         for (int i = 0; i < NK; ++i) xs[i] = x[i];
-        lq_median_slow<NT, NK, CAP, BP>(xs, elig, n, have_lo, lo, b, hist, sh, list, redbuf, res, g);
+        lq_median_slow<NT, NK, CAP, BP>(xs, elig, n, have_lo, lo, a, b, hist, sh, list, redbuf, res, g);
         lo = res[0]; hi = res[1]; b = res[2];
     }
     if (n & 1) hi = lo;
     lo_out = lo; hi_out = hi;
-    // next frame's window: centred on this median (a wild value just costs that frame a relocation)
-    const float nb = __fsub_rn(0.5f, __fmul_rn(psr_mid(lo, hi), LQ_A));
-    bcen = fabsf(nb) < 1.0e6f ? nb : 0.5f;
+    float na = a;
+    if (tails * 2 > n) na = a * 0.25f;
+    else if (tails * 8 > n) na = a * 0.5f;
+    else if (M > 96 && tails * 32 < n) na = a * 2.0f;
+    na = fminf(fmaxf(na, LQ_A_MIN), LQ_A);
+    const float nb = __fsub_rn(0.5f, __fmul_rn(psr_mid(lo, hi), na));                     // a wild value just costs that frame a relocation
+    win.a = na; win.b = fabsf(nb) < 1.0e6f ? nb : 0.5f;
     return true;
 }
 
@@ -1094,10 +971,11 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     constexpr int TR = ROWS / 2, TC = COLS / NB, CH = TC / CW, NCH = TR * CH, CPT = NCH / NT, NK = CPT * CW;   // CW = pixels per chunk (4 or 8)
     constexpr int NW = NT / 32;
     static_assert(NCH % NT == 0 && NT % 32 == 0 && NK <= 32, "tile must split evenly over the CTA");
+    constexpr int CAP = NT > 512 ? 512 : NT;
     __shared__ int redbuf[64];
-    __shared__ uint32_t hist[2048];
-    __shared__ uint32_t list[LISTCAP + 32];
-    __shared__ int selsh[40];
+    __shared__ __align__(16) uint32_t hist[LQ_NB];
+    __shared__ __align__(16) float list[CAP + 4];
+    __shared__ __align__(16) int selsh[48];
 
     const int tid = threadIdx.x;
     // Block order: bank fastest, then FRAME, then (half, segment).  The CTAs resident at one time then work on all frames of
@@ -1113,11 +991,13 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     const uint16_t* rawf = raw + (size_t)frame * c.npix;
     float* outf = out + (size_t)frame * (IMG ? (size_t)c.H * c.W : (size_t)c.npix);    // IMG: out is the batch of assembled images
 
-    // KS: the keys are parked in shared memory (slot q of thread t at skeys[q * NT + t]) instead of registers, which
+    // KS: the values are parked in shared memory (slot q of thread t at sx[q * NT + t]) instead of registers, which
     // buys another resident CTA per SM
-    extern __shared__ uint32_t skeys[];
-    uint32_t keyr[KS ? 1 : NK];
-    SmemKeys<NT> keys{skeys + tid};
+    extern __shared__ float sx[];
+    float xr[KS ? 1 : NK];
+    const SmemVals<NT> xs{sx + tid};
+    for (int i = tid; i < LQ_NB; i += NT) hist[i] = 0u;
+    __syncthreads();
     uint32_t elig = 0, sel0 = 0, sel1 = 0;
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
@@ -1156,7 +1036,7 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
                 if (c.offs != nullptr) x = __fsub_rn(x, off);
                 el = (sel < 3 && ((c.elig_mask >> sel) & 1u) && (f & PSR_FL_MASK)) ? 1u : 0u;
             }
-            if constexpr (KS) skeys[q * NT + tid] = psr_f2key(x); else keyr[q] = psr_f2key(x);
+            if constexpr (KS) sx[q * NT + tid] = x; else xr[q] = x;
             elig |= (el ? 1u : 0u) << q;
             sel0 |= (sel & 1u) << q;
             if (DET != 0) sel1 |= (sel >> 1) << q;
@@ -1164,14 +1044,13 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     }
 
     // common_mode_2d: skip if n < npix_min, skip if |cm| > cormax
-    BlockRed<NW> red{redbuf, 0};
-    const int n = red.sum(__popc(elig));
-    float cm = 0.f; bool apply = false;
-    if (n >= c.npix_min && n > 0) {                        // uniform across the CTA
-        uint32_t lo, hi;
-        if constexpr (KS) block_median_keys<NT, NK, NW>(keys, elig, n, hist, selsh, list, red, lo, hi);
-        else block_median_keys<NT, NK, NW>(keyr, elig, n, hist, selsh, list, red, lo, hi);
-        cm = psr_mid(psr_key2f(lo), psr_key2f(hi));
+    float cm = 0.f, lo, hi; bool apply = false;
+    LqWindow win{LQ_A, 0.5f};
+    bool have;
+    if constexpr (KS) have = block_median_linear<NT, NK, CAP, BitsLinear>(xs, elig, c.npix_min, win, hist, selsh, list, redbuf, lo, hi, CtaGroup{});
+    else have = block_median_linear<NT, NK, CAP, BitsLinear>(xr, elig, c.npix_min, win, hist, selsh, list, redbuf, lo, hi, CtaGroup{});
+    if (have) {                                            // uniform across the CTA
+        cm = psr_mid(lo, hi);
         apply = !(fabsf(cm) > c.cormax);
     }
 
@@ -1194,7 +1073,7 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
             const int q = j * CW + i;
             const uint32_t f = (fw[i >> 2] >> (8 * (i & 3))) | (c.ignore_keep ? PSR_FL_KEEP : 0u);
             float x;
-            if constexpr (KS) x = psr_key2f(keys[q]); else x = psr_key2f(keyr[q]);
+            if constexpr (KS) x = xs[q]; else x = xr[q];
             if (apply && ((elig >> q) & 1u)) x = __fsub_rn(x, cm);
             const uint32_t sel = ((sel0 >> q) & 1u) | (((sel1 >> q) & 1u) << 1);
             float gf;
@@ -1214,455 +1093,9 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
 }
 
 // =================================================================================================
-// epix10ka, mode 4, FRAMES-INNER: a CTA owns one bank tile and walks `fpc` frames of the batch.  The
-// tile's pedestals (both bit-14 entries, 67.6 KB) are staged ONCE in shared memory -- each thread only
-// ever reads the slots of its own 24 pixels, so no barrier guards them -- and the per-pixel flag bits
-// (mask, keep, eligibility for either bit-14 state) sit in four registers as 24-bit planes, so that a
-// frame's eligibility is one logic operation on the plane of its bit-14 states.  The values stay in
-// registers as floats from load to store; the median comes from block_median_linear.  The gain factors
-// of the epilogue come from L2.
-// =================================================================================================
-template <int NT, int MINB, bool IMG>
-__global__ void __launch_bounds__(NT, MINB)
-cm_banks_epix_fi_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c, int nframes, int fpc)
-{
-    constexpr int ROWS = 352, COLS = 384, NB = 8, TR = ROWS / 2, TC = COLS / NB, CH = TC / 8, NCH = TR * CH, CPT = NCH / NT, NK = CPT * 8;
-    constexpr int CAP = NT / 4 * 4;
-    using BP = BitsEpixWords;
-    static_assert(NCH % NT == 0 && NT % 32 == 0 && CPT <= 3, "tile must split evenly over the CTA; bit planes hold 3 chunks");
-    extern __shared__ float4 sm4[];                               // [4][NCH]: ped0 px0-3, ped0 px4-7, ped1 px0-3, ped1 px4-7
-    int* sgp = reinterpret_cast<int*>(sm4 + 4 * NCH);             // [CPT][NT] first pixel of a thread's chunk; IMG: + [CPT][NT] its image index
-    __shared__ int redbuf[64];
-    __shared__ __align__(16) uint32_t hist[LQ_NB];
-    __shared__ __align__(16) float list[CAP + 4];
-    __shared__ __align__(16) int selsh[48];
-
-    const int tid = threadIdx.x;
-    int bid = blockIdx.x;
-    const int bank = bid % NB; bid /= NB;
-    const int half = bid & 1;  bid >>= 1;
-    const int seg = bid;
-    const int f_begin = blockIdx.y * fpc, f_end = min(nframes, f_begin + fpc);
-
-    for (int i = tid; i < LQ_NB; i += NT) hist[i] = 0u;
-    uint32_t kbits = 0, e0bits = 0, e1bits = 0;                   // bit BP::pos(i) = value i of this thread
-    uint32_t kinds = 0;                                           // IMG: where each chunk goes in the assembled image is the same for every frame
-#pragma unroll
-    for (int j = 0; j < CPT; ++j) {
-        const int ch = tid + j * NT;
-        const int r = ch / CH, cc = ch - r * CH;
-        const int gp = ((seg * ROWS + half * TR + r) * COLS) + bank * TC + cc * 8;
-        sgp[j * NT + tid] = gp;
-        sm4[0 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped0 + gp));
-        sm4[1 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped0 + gp) + 1);
-        sm4[2 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped1 + gp));
-        sm4[3 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped1 + gp) + 1);
-        const uint2 f = __ldg(reinterpret_cast<const uint2*>(c.flags + gp));
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const uint32_t fb = ((i < 4 ? f.x : f.y) >> (8 * (i & 3))) & 0xFFu;
-            const int q = BP::pos(j * 8 + i);
-            kbits |= ((fb & PSR_FL_KEEP) ? 1u : 0u) << q;
-            e0bits |= ((fb & PSR_FL_ELIG0) ? 1u : 0u) << q;
-            e1bits |= ((fb & PSR_FL_ELIG1) ? 1u : 0u) << q;
-        }
-        if constexpr (IMG) {
-            int t0; kinds |= img_chunk_kind<8>(c.fwd + gp, t0) << (2 * j);
-            sgp[(CPT + j) * NT + tid] = t0;
-        }
-    }
-    const bool use_keep = c.has_keep && !c.ignore_keep;           // uniform: np.where(keep, v, 0) only when a keep mask is installed
-    const size_t fout = IMG ? (size_t)c.H * c.W : (size_t)c.npix;
-    // always 0 (this kernel is epix10ka's), but not to the compiler: lets a value be made to depend on another, which
-    // keeps ptxas from hoisting every chunk's loads to the top and spilling the values it has already computed
-    const uint32_t zero = (uint32_t)c.det_kind;
-    __syncthreads();
-
-    float bcen = 0.5f;                                            // histogram window centred on 0, then on the previous frame's median
-    for (int frame = f_begin; frame < f_end; ++frame) {
-        const uint16_t* rawf = raw + (size_t)frame * c.npix;
-        float* outf = out + (size_t)frame * fout;
-        float x[NK];
-        uint32_t sbits = 0;                                       // bit BP::pos(i) = data bit 14 of value i
-        asm volatile("" : "+r"(kbits));                           // not loop-invariant to the compiler: it would hoist (and spill) 24 single-bit tests
-        uint4 rv[CPT];
-#pragma unroll
-        for (int j = 0; j < CPT; ++j) rv[j] = __ldcs(reinterpret_cast<const uint4*>(rawf + sgp[j * NT + tid]));
-        uint32_t chain = 0;
-#pragma unroll
-        for (int j = 0; j < CPT; ++j) {
-            const int ch = tid + j * NT + (int)chain;             // chunk j's pedestals are fetched once chunk j - 1 is done
-            const uint32_t w[4] = {rv[j].x, rv[j].y, rv[j].z, rv[j].w};
-            const float4 a0 = sm4[0 * NCH + ch], a1 = sm4[1 * NCH + ch], b0 = sm4[2 * NCH + ch], b1 = sm4[3 * NCH + ch];
-            const float pa[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-            const float pb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                // both bit-14 flags of the word with one shift: bit 14 -> 4j + k, bit 30 -> 16 + 4j + k
-                sbits |= (w[k] >> (14 - 4 * j - k)) & (0x00010001u << (4 * j + k));
-#if PSR_CMF_MAGIC
-                const uint32_t wm = w[k] & 0x3FFF3FFFu;
-                // float(v) without a conversion: 0x4B000000 | v is 2^23 + v; both subtractions are exact or correctly rounded
-                const float fe = __fsub_rn(__uint_as_float(__byte_perm(wm, 0x4B000000u, 0x7610)), 8388608.0f);
-                const float fo = __fsub_rn(__uint_as_float(__byte_perm(wm, 0x4B000000u, 0x7632)), 8388608.0f);
-#else
-                const float fe = (float)(w[k] & 0x3FFFu), fo = (float)((w[k] >> 16) & 0x3FFFu);
-#endif
-                x[j * 8 + 2 * k] = psr_sub_sel(fe, pa[2 * k], pb[2 * k], w[k] & 0x4000u);
-                x[j * 8 + 2 * k + 1] = psr_sub_sel(fo, pa[2 * k + 1], pb[2 * k + 1], w[k] & 0x40000000u);
-            }
-#if PSR_CMF_CHAIN
-            chain = __float_as_uint(x[j * 8 + 7]) & zero;
-#endif
-        }
-        const uint32_t elig = (sbits & e1bits) | (~sbits & e0bits);
-
-        // common_mode_2d: skip if n < npix_min, skip if |cm| > cormax.  An unapplied correction is cm = +0: x - 0 == x for every x.
-        float lo, hi, cm = 0.f;
-        if (block_median_linear<NT, NK, CAP, BP>(x, elig, c.npix_min, bcen, hist, selsh, list, redbuf, lo, hi, CtaGroup{})) {      // uniform
-            const float med = psr_mid(lo, hi);
-            if (!(fabsf(med) > c.cormax)) cm = med;
-        }
-
-        chain = 0;
-#pragma unroll
-        for (int j = 0; j < CPT; ++j) {
-            const int gp = sgp[j * NT + tid] + (int)chain;        // one chunk's gain factors in registers at a time
-            float o[8];
-            // the mask is folded into the gain factors (psr_set_constants): a masked pixel's factor is +-0
-            float g0[8], g1[8];
-            ld8(c.gf0 + gp, g0); ld8(c.gf1 + gp, g1);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int q = BP::pos(j * 8 + i);
-                const float xv = psr_sub_if(x[j * 8 + i], cm, elig & (1u << q));
-                o[i] = psr_mul_sel(xv, g0[i], g1[i], sbits & (1u << q));
-            }
-            if (use_keep) {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) if (!(kbits & (1u << BP::pos(j * 8 + i)))) o[i] = 0.0f;
-            }
-#if PSR_CMF_CHAIN
-            chain = __float_as_uint(o[7]) & zero;
-#endif
-            if constexpr (IMG) img_store_chunk<8>(outf, c.fwd + gp, (kinds >> (2 * j)) & 3u, sgp[(CPT + j) * NT + tid], o);
-            else {
-                __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
-                __stcs(reinterpret_cast<float4*>(outf + gp + 4), make_float4(o[4], o[5], o[6], o[7]));
-            }
-        }
-    }
-}
-
-// =================================================================================================
-// epix10ka, mode 4, FRAME PAIRS: one 704-thread CTA per SM owns one bank tile and walks `fpc` frames of the
-// batch two at a time.  ALL of the tile's constants (both pedestal and both gain-factor entries, 135 KB)
-// are staged once in shared memory -- a thread only ever reads the slots of its own 12 pixels, so no
-// barrier guards them -- so the frame loop's global traffic is raw in and floats out, nothing else.  A
-// thread holds 12 pixels of each of the two frames (24 values, as floats, from load to store) and the
-// per-pixel flag bits as register planes.  Two frames per pass through the phases (histogram, scan,
-// collect, rank) halves the barriers per frame, doubles the independent work between them and lets the
-// two scans and the two rankings run on different warps at the same time.
-// =================================================================================================
-// value i = pixel (2k + h) of 4-pixel chunk j (i = 4j + 2k + h: word k of the chunk's two raw words, low / high half):
-// bit 2j + k + 16h, the place where ONE shift of the raw word drops its two bit-14 flags
-struct BitsEpixWords4 { static __device__ __forceinline__ constexpr int pos(int i) { return 2 * (i >> 2) + ((i & 3) >> 1) + 16 * (i & 1); } };
-
-template <bool IMG, int NF>
-__global__ void __launch_bounds__(704, 1)
-cm_banks_epix_pair_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c, int nframes, int fpc)
-{
-    constexpr int NT = 704, ROWS = 352, COLS = 384, NB = 8, TR = ROWS / 2, TC = COLS / NB, CH = TC / 4, NCH = TR * CH, CPT = NCH / NT, NK = CPT * 4;
-    constexpr int CAP = NT / NF, NSCAN = LQ_NB / 8;
-    using BP = BitsEpixWords4;
-    static_assert(NCH % NT == 0 && NT >= NF * NSCAN && CAP % 4 == 0, "tile / scan / rank layout");
-    extern __shared__ float4 sm4[];                               // [4][NCH]: ped0, ped1, gf0, gf1 of the 4 pixels of a chunk
-    int* sgp = reinterpret_cast<int*>(sm4 + 4 * NCH);             // [CPT][NT] first pixel of a thread's chunk; IMG: + [CPT][NT] its image index
-    uint2* sraw = reinterpret_cast<uint2*>(sgp + 2 * CPT * NT);   // [NF][CPT][NT] the next pair's raw chunks, staged by cp.async (each thread its own)
-    // the second frame's values wait here between the phases (each thread its own slots) instead of in 12 more registers,
-    // which ptxas would spill to local memory one by one
-    float4* park = reinterpret_cast<float4*>(sraw + (PSR_PAIR_STAGE ? NF * CPT * NT : 0));      // [CPT][NT]
-    constexpr bool PARK = PSR_PAIR_PARK && NF == 2;
-    __shared__ int redbuf[64];
-    __shared__ __align__(16) uint32_t hist[NF][LQ_NB];
-    __shared__ __align__(16) float list[NF][CAP + 4];
-    __shared__ __align__(16) int selsh[NF][48];
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    int bid = blockIdx.x;
-    const int bank = bid % NB; bid /= NB;
-    const int half = bid & 1;  bid >>= 1;
-    const int seg = bid;
-    const int f_begin = blockIdx.y * fpc, f_end = min(nframes, f_begin + fpc);
-
-    for (int i = tid; i < NF * LQ_NB; i += NT) (&hist[0][0])[i] = 0u;
-    uint32_t kbits = 0, e0bits = 0, e1bits = 0;                   // bit BP::pos(i) = value i of this thread
-    uint32_t kinds = 0;                                           // IMG: where each chunk goes in the assembled image is the same for every frame
-#pragma unroll
-    for (int j = 0; j < CPT; ++j) {
-        const int ch = tid + j * NT;
-        const int r = ch / CH, cc = ch - r * CH;
-        const int gp = ((seg * ROWS + half * TR + r) * COLS) + bank * TC + cc * 4;
-        sgp[j * NT + tid] = gp;
-        // the mask is folded into the gain factors (psr_set_constants): a masked pixel's factor is +-0
-        sm4[0 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped0 + gp));
-        sm4[1 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped1 + gp));
-        sm4[2 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.gf0 + gp));
-        sm4[3 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.gf1 + gp));
-        const uint32_t f = __ldg(reinterpret_cast<const uint32_t*>(c.flags + gp));
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const uint32_t fb = (f >> (8 * i)) & 0xFFu;
-            const int q = BP::pos(j * 4 + i);
-            kbits |= ((fb & PSR_FL_KEEP) ? 1u : 0u) << q;
-            e0bits |= ((fb & PSR_FL_ELIG0) ? 1u : 0u) << q;
-            e1bits |= ((fb & PSR_FL_ELIG1) ? 1u : 0u) << q;
-        }
-        if constexpr (IMG) {
-            int t0; kinds |= img_chunk_kind<4>(c.fwd + gp, t0) << (2 * j);
-            sgp[(CPT + j) * NT + tid] = t0;
-        }
-    }
-    const bool use_keep = c.has_keep && !c.ignore_keep;           // uniform: np.where(keep, v, 0) only when a keep mask is installed
-    const size_t fout = IMG ? (size_t)c.H * c.W : (size_t)c.npix;
-#if PSR_PAIR_STAGE
-    if (f_begin < f_end) {                                        // the first pair's raw chunks
-#pragma unroll
-        for (int g = 0; g < NF; ++g) {
-            const int fr = min(f_begin + g, f_end - 1);
-#pragma unroll
-            for (int j = 0; j < CPT; ++j)
-                psr_cp_async8(&sraw[(g * CPT + j) * NT + tid], raw + (size_t)fr * c.npix + sgp[j * NT + tid]);
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    }
-#endif
-    __syncthreads();
-
-    float bcen[NF];                                               // histogram windows: centred on 0, then on the previous median of the same slot
-#pragma unroll
-    for (int f = 0; f < NF; ++f) bcen[f] = 0.5f;
-    for (int frame = f_begin; frame < f_end; frame += NF) {
-        const bool pair = NF > 1 && frame + 1 < f_end;            // an odd tail runs its frame twice and stores it once
-        float x[NF][NK];
-        uint32_t sbits[NF], elig[NF];
-        asm volatile("" : "+r"(kbits));                           // not loop-invariant to the compiler: it would hoist (and spill) the single-bit tests
-#pragma unroll
-        for (int f = 0; f < NF; ++f) {
-            uint2 rv[CPT];
-#if PSR_PAIR_STAGE
-            // this pair's raw chunks were staged in shared memory while the previous pair was processed (thread-private
-            // slots: the thread's own wait_group is all the ordering needed); then the next pair's copies are started
-            if (f == 0) asm volatile("cp.async.wait_group 0;" ::: "memory");
-#pragma unroll
-            for (int j = 0; j < CPT; ++j) rv[j] = sraw[(f * CPT + j) * NT + tid];
-            if (f == NF - 1 && frame + NF < f_end) {
-#pragma unroll
-                for (int g = 0; g < NF; ++g) {
-                    const int fr = min(frame + NF + g, f_end - 1);                // an odd tail stages its frame twice
-#pragma unroll
-                    for (int j = 0; j < CPT; ++j)
-                        psr_cp_async8(&sraw[(g * CPT + j) * NT + tid], raw + (size_t)fr * c.npix + sgp[j * NT + tid]);
-                }
-                asm volatile("cp.async.commit_group;" ::: "memory");
-            }
-#else
-            const uint16_t* rawf = raw + (size_t)(frame + ((f == 1 && pair) ? 1 : 0)) * c.npix;
-#pragma unroll
-            for (int j = 0; j < CPT; ++j) rv[j] = __ldcs(reinterpret_cast<const uint2*>(rawf + sgp[j * NT + tid]));
-#if PSR_PAIR_PREFETCH
-            if (f == 0 && frame + NF < f_end) {                   // next pair's raw tiles on their way into L2 meanwhile
-#pragma unroll
-                for (int j = 0; j < CPT; ++j) {
-                    asm volatile("prefetch.global.L2 [%0];" :: "l"(rawf + (size_t)NF * c.npix + sgp[j * NT + tid]));
-                    if (NF > 1) asm volatile("prefetch.global.L2 [%0];" :: "l"(rawf + (size_t)(NF + 1) * c.npix + sgp[j * NT + tid]));
-                }
-            }
-#endif
-#endif
-            uint32_t sb = 0;
-#pragma unroll
-            for (int j = 0; j < CPT; ++j) {
-                const int ch = tid + j * NT;
-                const uint32_t w[2] = {rv[j].x, rv[j].y};
-                const float4 p0 = sm4[0 * NCH + ch], p1 = sm4[1 * NCH + ch];
-                const float pa[4] = {p0.x, p0.y, p0.z, p0.w}, pb[4] = {p1.x, p1.y, p1.z, p1.w};
-#pragma unroll
-                for (int k = 0; k < 2; ++k) {
-                    // both bit-14 flags of the word with one shift: bit 14 -> 2j + k, bit 30 -> 16 + 2j + k
-                    sb |= (w[k] >> (14 - 2 * j - k)) & (0x00010001u << (2 * j + k));
-                    const uint32_t wm = w[k] & 0x3FFF3FFFu;
-                    // float(v) without a conversion: 0x4B000000 | v is 2^23 + v; both subtractions are exact or correctly rounded
-                    const float fe = __fsub_rn(__uint_as_float(__byte_perm(wm, 0x4B000000u, 0x7610)), 8388608.0f);
-                    const float fo = __fsub_rn(__uint_as_float(__byte_perm(wm, 0x4B000000u, 0x7632)), 8388608.0f);
-                    x[f][j * 4 + 2 * k] = psr_sub_sel(fe, pa[2 * k], pb[2 * k], w[k] & 0x4000u);
-                    x[f][j * 4 + 2 * k + 1] = psr_sub_sel(fo, pa[2 * k + 1], pb[2 * k + 1], w[k] & 0x40000000u);
-                }
-            }
-            sbits[f] = sb;
-            elig[f] = (sb & e1bits) | (~sb & e0bits);
-        }
-
-        // ---- the two medians (common_mode_2d: skip if n < npix_min, skip if |cm| > cormax) -------------------------
-        // histograms
-#pragma unroll
-        for (int f = 0; f < NF; ++f) {
-            const uint32_t cadd = (uint32_t)__cvta_generic_to_shared(&hist[f][0]) - 0x2C000000u;      // bits(2^23) * 4 mod 2^32
-#pragma unroll
-            for (int i = 0; i < NK; ++i) {
-                const uint32_t ad = lq_bits(x[f][i], LQ_A, bcen[f]) * 4u + cadd;
-                const uint32_t m = (elig[f] << (31 - BP::pos(i))) >> 31;                              // ineligible: add 0 (no branch around the atomic)
-                asm volatile("red.shared.add.u32 [%0], %1;" :: "r"(ad), "r"(m) : "memory");
-            }
-            if (PARK && f == 1) {
-#pragma unroll
-                for (int j = 0; j < CPT; ++j) park[j * NT + tid] = make_float4(x[1][j * 4], x[1][j * 4 + 1], x[1][j * 4 + 2], x[1][j * 4 + 3]);
-            }
-        }
-        __syncthreads();
-        // scans: warps 0-7 take frame 0's bins, warps 8-15 frame 1's
-        const int sf = warp >> 3, st = tid - sf * NSCAN;          // scanning frame / thread within the scan (valid for warp < 16)
-        uint32_t bn[8]; uint32_t ssum = 0, incl = 0;
-        if (warp < NF * (NSCAN / 32)) {
-            uint4* h4 = reinterpret_cast<uint4*>(&hist[sf][0]) + 2 * st;
-            const uint4 u = h4[0], v = h4[1];
-            h4[0] = make_uint4(0, 0, 0, 0); h4[1] = make_uint4(0, 0, 0, 0);                           // the owner leaves its bins zero
-            bn[0] = u.x; bn[1] = u.y; bn[2] = u.z; bn[3] = u.w; bn[4] = v.x; bn[5] = v.y; bn[6] = v.z; bn[7] = v.w;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) ssum += bn[j];
-            incl = ssum;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
-            if (lane == 31) selsh[sf][warp & 7] = (int)incl;
-        }
-        __syncthreads();
-        if (warp < NF * (NSCAN / 32)) {
-            const int4 t0 = reinterpret_cast<const int4*>(&selsh[sf][0])[0], t1 = reinterpret_cast<const int4*>(&selsh[sf][0])[1];
-            const int tw[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
-            int n = 0; uint32_t base = 0;
-#pragma unroll
-            for (int w = 0; w < 8; ++w) { n += tw[w]; base += (w < (warp & 7)) ? (uint32_t)tw[w] : 0u; }
-            const int k1 = (n - 1) >> 1;
-            const uint32_t excl = base + incl - ssum;
-            if (n > 0 && (uint32_t)k1 >= excl && (uint32_t)k1 < excl + ssum) {
-                uint32_t rr = (uint32_t)k1 - excl; bool done = false;
-#pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    if (!done) { if (rr < bn[j]) { selsh[sf][32] = 8 * st + j; selsh[sf][33] = (int)rr; selsh[sf][34] = (int)bn[j]; done = true; } else rr -= bn[j]; }
-            }
-            if (st == 0) { selsh[sf][35] = 0; selsh[sf][36] = n; }
-        }
-        __syncthreads();
-        // collect the members of the two bins
-        int nn[NF], Bf[NF], rf[NF], Mf[NF]; bool fast[NF];
-#pragma unroll
-        for (int f = 0; f < NF; ++f) {
-            nn[f] = selsh[f][36]; Bf[f] = selsh[f][32]; rf[f] = selsh[f][33]; Mf[f] = selsh[f][34];
-            fast[f] = nn[f] >= c.npix_min && nn[f] >= 1 && Bf[f] > 0 && Bf[f] < LQ_NB - 1 && Mf[f] <= CAP;     // uniform
-            if (fast[f]) {
-                const uint32_t target = 0x4B000000u + (uint32_t)Bf[f];
-                uint32_t hits = 0; float cand = 0.f;
-                float bb = bcen[f];
-                asm volatile("" : "+f"(bb));                      // the bins are recomputed, not kept from the histogram pass (12 registers)
-                if (PARK && f == 1) {
-#pragma unroll
-                    for (int j = 0; j < CPT; ++j) { const float4 v = park[j * NT + tid]; x[1][j * 4] = v.x; x[1][j * 4 + 1] = v.y; x[1][j * 4 + 2] = v.z; x[1][j * 4 + 3] = v.w; }
-                }
-#pragma unroll
-                for (int i = 0; i < NK; ++i)
-                    if (lq_bits(x[f][i], LQ_A, bb) == target) { hits |= 1u << BP::pos(i); cand = x[f][i]; }
-                // a thread almost never holds two members of the bin: one candidate register, one branch per thread
-                if (hits != 0u) {
-                    if ((hits & (hits - 1u)) == 0u) { if (hits & elig[f]) list[f][atomicAdd(&selsh[f][35], 1)] = cand; }
-                    else {
-                        hits &= elig[f];
-#pragma unroll
-                        for (int i = 0; i < NK; ++i) if (hits & (1u << BP::pos(i))) list[f][atomicAdd(&selsh[f][35], 1)] = x[f][i];
-                    }
-                }
-                if (tid < 4) list[f][Mf[f] + tid] = __int_as_float(0x7f800000);                       // pad to a multiple of four
-            }
-        }
-        __syncthreads();
-        // rank: threads [0, M0) take frame 0's list, threads [CAP, CAP + M1) frame 1's
-        {
-            const bool f1 = NF > 1 && tid >= CAP;
-            const int t = f1 ? tid - CAP : tid, M = f1 ? Mf[NF - 1] : Mf[0], r = f1 ? rf[NF - 1] : rf[0];
-            const bool on = f1 ? fast[NF - 1] : fast[0];
-            const float* lst = f1 ? &list[NF - 1][0] : &list[0][0];
-            int* shf = f1 ? &selsh[NF - 1][0] : &selsh[0][0];
-            if (on && t < M) {
-                const float v = lst[t];
-                int lt = 0, le = 0;
-                for (int j = 0; j < M; j += 4) {
-                    const float4 u = *reinterpret_cast<const float4*>(lst + j);
-                    lt += (u.x < v) + (u.y < v) + (u.z < v) + (u.w < v);
-                    le += (u.x <= v) + (u.y <= v) + (u.z <= v) + (u.w <= v);
-                }
-                if (lt <= r && r < le) shf[37] = __float_as_int(v);
-                if (lt <= r + 1 && r + 1 < le) shf[38] = __float_as_int(v);
-            }
-        }
-        __syncthreads();
-        float cm[NF];
-#pragma unroll
-        for (int f = 0; f < NF; ++f) {
-            cm[f] = 0.f;                                          // an unapplied correction is cm = +0: x - 0 == x for every x
-            if (nn[f] >= c.npix_min && nn[f] >= 1) {              // uniform
-                float lo = __int_as_float(selsh[f][37]);
-                const bool have_hi = rf[f] + 1 < Mf[f];
-                float hi = have_hi ? __int_as_float(selsh[f][38]) : lo;
-                if (!fast[f] || (!have_hi && (nn[f] & 1) == 0)) { // uniform, rare: everything unusual, on a copy in local memory
-                    float xs[NK], res[3];
-#pragma unroll
-                    for (int i = 0; i < NK; ++i) xs[i] = (PARK && f == 1) ? reinterpret_cast<const float*>(&park[(i >> 2) * NT + tid])[i & 3] : x[f][i];
-                    lq_median_slow<NT, NK, CAP, BP>(xs, elig[f], nn[f], fast[f], lo, bcen[f], &hist[f][0], &selsh[f][0], &list[f][0], redbuf, res, CtaGroup{});
-                    lo = res[0]; hi = res[1];
-                }
-                if (nn[f] & 1) hi = lo;
-                const float med = psr_mid(lo, hi);
-                if (!(fabsf(med) > c.cormax)) cm[f] = med;
-                const float nb = __fsub_rn(0.5f, __fmul_rn(med, LQ_A));       // next window: centred on this median
-                bcen[f] = fabsf(nb) < 1.0e6f ? nb : 0.5f;
-            }
-        }
-
-        // ---- gain, keep, store ---------------------------------------------------------------------------------------
-#pragma unroll
-        for (int f = 0; f < NF; ++f) {
-            if (f == 1 && !pair) break;
-            float* outf = out + (size_t)(frame + f) * fout;
-            asm volatile("" : "+r"(elig[f]), "+r"(sbits[f]));     // single-bit tests are made here, not carried (spilled) from the load phase
-#pragma unroll
-            for (int j = 0; j < CPT; ++j) {
-                const int ch = tid + j * NT;
-                const float4 ga = sm4[2 * NCH + ch], gb = sm4[3 * NCH + ch];
-                const float g0[4] = {ga.x, ga.y, ga.z, ga.w}, g1[4] = {gb.x, gb.y, gb.z, gb.w};
-                float o[8];
-                float xj[4];
-                if (PARK && f == 1) { const float4 v = park[j * NT + tid]; xj[0] = v.x; xj[1] = v.y; xj[2] = v.z; xj[3] = v.w; }
-                else { xj[0] = x[f][j * 4]; xj[1] = x[f][j * 4 + 1]; xj[2] = x[f][j * 4 + 2]; xj[3] = x[f][j * 4 + 3]; }
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int q = BP::pos(j * 4 + i);
-                    const float xv = psr_sub_if(xj[i], cm[f], elig[f] & (1u << q));
-                    o[i] = psr_mul_sel(xv, g0[i], g1[i], sbits[f] & (1u << q));
-                }
-                if (use_keep) {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) if (!(kbits & (1u << BP::pos(j * 4 + i)))) o[i] = 0.0f;
-                }
-                const int gp = sgp[j * NT + tid];
-                if constexpr (IMG) img_store_chunk<4>(outf, c.fwd + gp, (kinds >> (2 * j)) & 3u, sgp[(CPT + j) * NT + tid], o);
-                else __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
-            }
-        }
-    }
-}
-
-// =================================================================================================
-// epix10ka, mode 4, TWO FRAME GROUPS: as the frame-pair kernel (one 704-thread CTA per SM, all of the bank
-// tile's constants staged once in shared memory), but the CTA is two groups of 352 threads that each take
+// epix10ka, mode 4, TWO FRAME GROUPS: one 704-thread CTA per SM owns one bank tile and walks `fpc` frames of the
+// batch, with ALL of the tile's constants (both pedestal and both gain-factor entries, 135 KB) staged once in
+// shared memory, so the frame loop's global traffic is raw in and floats out, nothing else.  The CTA is two groups of 352 threads that each take
 // every other frame of the CTA's share and synchronise only among themselves (hardware barriers 1 and 2):
 // the groups drift apart and fill each other's barrier and latency gaps, like two CTAs that share their
 // 135 KB of constants.  A thread holds 24 pixels (six 4-pixel chunks) of its group's frame.
@@ -1732,7 +1165,7 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
     __syncthreads();
 
     const WarpGroup<GT> g{t, 1 + grp};
-    float bcen = 0.5f;                                            // histogram window centred on 0, then on the group's previous median
+    LqWindow win{LQ_A, 0.5f};                                     // 64 ADU centred on 0, then following the group's medians and their spread
     for (int frame = f_begin + grp; frame < f_end; frame += NG) {
         const uint16_t* rawf = raw + (size_t)frame * c.npix;
         float* outf = out + (size_t)frame * fout;
@@ -1776,7 +1209,7 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
 
         // common_mode_2d: skip if n < npix_min, skip if |cm| > cormax.  An unapplied correction is cm = +0: x - 0 == x for every x.
         float lo, hi, cm = 0.f;
-        if (block_median_linear<GT, NK, CAP, BP>(x, elig, c.npix_min, bcen, &hist[grp][0], &selsh[grp][0], &list[grp][0], &redbuf[grp][0], lo, hi, g)) {
+        if (block_median_linear<GT, NK, CAP, BP>(x, elig, c.npix_min, win, &hist[grp][0], &selsh[grp][0], &list[grp][0], &redbuf[grp][0], lo, hi, g)) {
             const float med = psr_mid(lo, hi);
             if (!(fabsf(med) > c.cormax)) cm = med;
         }
@@ -1827,21 +1260,10 @@ constexpr int EPIX_NT = 352, JF_NT = 512;
 #endif
 constexpr size_t EPIX_SMEM = ((size_t)(176 * 49) * 5 + 15) / 16 * 16 + (EPIX_NT / 32) * 4 * 256 * 4;   // padded tile (float + flag byte) + warp histograms
 constexpr size_t JF_SMEM = ((size_t)(256 * 65) * 5 + 15) / 16 * 16 + (JF_NT / 32) * 4 * 256 * 4;
-constexpr size_t EPIX_FI_SMEM = (size_t)1056 * (4 * 16) + (size_t)6 * 352 * 4;   // pedestals of one bank tile + per-thread chunk offsets
-#ifndef PSR_CM_FPC
-#define PSR_CM_FPC 8           /* frames per CTA of the frames-inner common-mode kernel */
-#endif
-#ifndef PSR_CM_PAIR
-#define PSR_CM_PAIR 1          /* epix10ka bank medians: 1 = frame-pair kernel (704 threads, all constants in shared memory) */
-#endif
-#ifndef PSR_CM_GROUPS
-#define PSR_CM_GROUPS 1        /* epix10ka bank medians: 1 = two-frame-group kernel instead of the frame-pair kernel */
+#ifndef PSR_CM_GROUPS_FPC
+#define PSR_CM_GROUPS_FPC 16   /* frames per CTA of the two-frame-group kernel (8 per group) */
 #endif
 constexpr size_t EPIX_GROUPS_SMEM = (size_t)2112 * (4 * 16) + (size_t)12 * 352 * 4;   // all four constant tables of one bank tile + per-thread chunk offsets
-#ifndef PSR_CM_PAIR_FPC
-#define PSR_CM_PAIR_FPC 16     /* frames per CTA of the frame-pair kernel */
-#endif
-constexpr size_t EPIX_PAIR_SMEM = (size_t)2112 * (4 * 16) + (size_t)6 * 704 * 4 + (PSR_PAIR_STAGE ? (size_t)2 * 3 * 704 * 8 : 0) + (PSR_PAIR_PARK ? (size_t)3 * 704 * 16 : 0);   // all four constant tables of one bank tile + per-thread chunk offsets + a pair of raw tiles
 
 }  // namespace
 
@@ -1860,14 +1282,6 @@ cudaError_t psr_common_mode_setup(void)
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(cm_banks_epix_groups_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_GROUPS_SMEM);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(cm_banks_epix_pair_kernel<false, PSR_PAIR_NF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_PAIR_SMEM);
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(cm_banks_epix_pair_kernel<true, PSR_PAIR_NF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_PAIR_SMEM);
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(cm_banks_epix_fi_kernel<EPIX_NT, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_FI_SMEM);
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(cm_banks_epix_fi_kernel<EPIX_NT, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_FI_SMEM);
-    if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(cm_calib_kernel<1, 512, 1024, 16, JF_NT>,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JF_SMEM);
 }
@@ -1877,15 +1291,10 @@ template <bool IMG>
 cudaError_t launch_banks(const PsrDev& c, const uint16_t* d_raw, int nframes, float* d_out, cudaStream_t st)
 {
     if (c.det_kind == 0) {
-        if (PSR_CM_PAIR && nframes > 1) {
-            const int fpc = PSR_CM_PAIR_FPC;
+        if (nframes > 1) {
+            const int fpc = PSR_CM_GROUPS_FPC;
             dim3 g2((unsigned)c.nseg * 2 * 8, (unsigned)((nframes + fpc - 1) / fpc));
-            if (PSR_CM_GROUPS) cm_banks_epix_groups_kernel<IMG><<<g2, 704, EPIX_GROUPS_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
-            else cm_banks_epix_pair_kernel<IMG, PSR_PAIR_NF><<<g2, 704, EPIX_PAIR_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
-        } else if (PSR_CM_FPC > 1 && nframes > 1) {
-            const int fpc = PSR_CM_FPC;
-            dim3 g2((unsigned)c.nseg * 2 * 8, (unsigned)((nframes + fpc - 1) / fpc));
-            cm_banks_epix_fi_kernel<EPIX_NT, 2, IMG><<<g2, EPIX_NT, EPIX_FI_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
+            cm_banks_epix_groups_kernel<IMG><<<g2, 704, EPIX_GROUPS_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
         } else {
             const unsigned grid = (unsigned)nframes * c.nseg * 2 * 8;
             cm_banks_kernel<0, 352, 384, 8, PSR_CMB_EPIX_NT, PSR_CMB_EPIX_MINB, PSR_CMB_EPIX_CW, PSR_CMB_EPIX_KS != 0, IMG>

@@ -126,12 +126,15 @@ class GpuCalibrator:
         Calls on one device share one scratch array: keep them on one stream.
         """
         import torch
-        if raw.dtype not in (torch.uint16, torch.int16) or not raw.is_contiguous() or not raw.is_cuda:
-            raise ValueError("raw must be a contiguous uint16/int16 CUDA tensor")
+        if raw.dtype not in (torch.uint16, torch.int16) or not raw.is_contiguous() or not raw.is_cuda or raw.device.index != self.device:
+            raise ValueError(f"raw must be a contiguous uint16/int16 tensor on cuda:{self.device}")
+        if tuple(raw.shape[1:]) != self.spec.shape:
+            raise ValueError(f"raw has frame shape {tuple(raw.shape[1:])}, expected {self.spec.shape}")
         nframes = raw.shape[0]
         shape = self.out_shape(nframes, True)
-        if tuple(out.shape) != shape or out.dtype != torch.float32 or not out.is_contiguous():
-            raise ValueError(f"out must be a contiguous float32 CUDA tensor of shape {shape}")
+        if (tuple(out.shape) != shape or out.dtype != torch.float32 or not out.is_contiguous()
+                or not out.is_cuda or out.device != raw.device):
+            raise ValueError(f"out must be a contiguous float32 tensor of shape {shape} on cuda:{self.device}")
         st = stream if stream is not None else torch.cuda.current_stream(raw.device).cuda_stream
         N.check(self._lib.psr_calib_image_noalloc(self._ctx, raw.data_ptr(), nframes, out.data_ptr(), st))
         return out
@@ -149,14 +152,48 @@ class GpuCalibrator:
         N.check(self._lib.psr_decode_gain_modes(self._ctx, raw.data_ptr(), nframes, out.data_ptr(), st))
         return out
 
+    def launches_per_batch(self, nframes: int, image: bool) -> int:
+        """Kernel launches one ``calib()`` call of this configuration makes (for launch accounting)."""
+        if not image:
+            return 1
+        if self.cm_mode in (0, 4):
+            return 2                    # scatter / fused common-mode kernel + the gap-fill kernel beside it
+        return 2                        # common mode into scratch + gather
+
     def calib_host(self, h_raw, h_out=None, d_out=None, image: bool = False):
-        """Host-fed form: ``h_raw`` is a NumPy array or CPU tensor (pinned for full speed)."""
+        """Host-fed form: ``h_raw`` is a NumPy array or CPU tensor (pinned for full speed), ``h_out`` likewise,
+        ``d_out`` a CUDA tensor on this calibrator's device.  Shapes, dtypes and contiguity are checked here: the
+        C ABI below takes bare pointers."""
+        def check_host(x, name, dtypes_np, dtypes_t, shape_tail):
+            if isinstance(x, np.ndarray):
+                ok = x.dtype in dtypes_np and x.flags["C_CONTIGUOUS"]
+            else:
+                ok = (not x.is_cuda) and x.dtype in dtypes_t and x.is_contiguous()
+            if not ok:
+                raise ValueError(f"{name} must be a C-contiguous host array of dtype {' / '.join(str(d) for d in dtypes_np)}")
+            if tuple(x.shape[1:]) != tuple(shape_tail):
+                raise ValueError(f"{name} has frame shape {tuple(x.shape[1:])}, expected {tuple(shape_tail)}")
+
         def ptr_n(x):
             if x is None:
                 return None, 0
             if isinstance(x, np.ndarray):
                 return x.ctypes.data, x.shape[0]
             return x.data_ptr(), x.shape[0]
+        import torch
+        if h_out is None and d_out is None:
+            raise ValueError("need h_out and/or d_out")
+        check_host(h_raw, "h_raw", (np.dtype(np.uint16), np.dtype(np.int16)), (torch.uint16, torch.int16), self.spec.shape)
+        nframes = h_raw.shape[0]
+        oshape = self.out_shape(nframes, image)
+        if h_out is not None:
+            check_host(h_out, "h_out", (np.dtype(np.float32),), (torch.float32,), oshape[1:])
+            if h_out.shape[0] != nframes:
+                raise ValueError(f"h_out holds {h_out.shape[0]} frames, h_raw {nframes}")
+        if d_out is not None:
+            if (not d_out.is_cuda or d_out.device.index != self.device or d_out.dtype != torch.float32
+                    or not d_out.is_contiguous() or tuple(d_out.shape) != oshape):
+                raise ValueError(f"d_out must be a contiguous float32 tensor of shape {oshape} on cuda:{self.device}")
         pr, n = ptr_n(h_raw)
         po, _ = ptr_n(h_out)
         pd = None if d_out is None else d_out.data_ptr()

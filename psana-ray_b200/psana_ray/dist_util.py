@@ -41,6 +41,18 @@ def max_over_ranks(seconds: float, device="cpu") -> float:
     return float(t.item())
 
 
+def gather_floats(value: float, device="cpu"):
+    """Every rank's value, on every rank (list of world_size floats)."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        return [float(value)]
+    t = torch.tensor([value], dtype=torch.float64, device=device)
+    out = [torch.zeros_like(t) for _ in range(dist.get_world_size())]
+    dist.all_gather(out, t)
+    return [float(o.item()) for o in out]
+
+
 def shard(nevents: int, rank: int, size: int):
     """Event numbers of one rank: nevent % size == rank."""
     return range(rank, nevents, size)

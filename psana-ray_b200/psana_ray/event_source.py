@@ -13,7 +13,8 @@ the producer calibrates whole batches on its GPU.
   * ``SyntheticSource`` -- seeded frames of the named detector shape (psana and the LCLS file
     system are not available offline); used by the CLI by default, by the tests and by bench.py.
   * ``PsanaSource`` -- the same interface over a real psana ``MPIDataSource`` + ``Detector``; only
-    importable where psana is installed; untested here.
+    importable where psana is installed.  Here it runs against ``tests/fake_psana``, a
+    stub of the psana calls it makes.
 """
 from __future__ import annotations
 
@@ -135,52 +136,154 @@ def epix10ka_config_bytes(pixel_config, trbits, asic_quadrants=((1, 1), (0, 1), 
     return cfg
 
 
-class PsanaSource:
-    """psana-backed source (LCLS-I psana1).  Needs ``import psana``; raises ImportError otherwise."""
+def _epix10ka_cfg_from_psana(det, env, source, shape):
+    """The (nseg, rows, cols) config bytes of an epix10ka-family detector from psana's own objects [EXT].
 
-    def __init__(self, exp, run, detector_name, rank=0, size=1, epix10ka_cfg=None):
+    psana's helper is preferred -- ``Detector.UtilsEpix10ka.cbits_config_epix10ka_any`` is what
+    ``gain_maps_epix10ka_any`` itself decodes, so its ASIC -> quadrant placement of the trbits is the
+    authoritative one.  Its call convention differs between psana releases (config object vs detector), so
+    both are tried; if the module has neither, the bytes are built here from the configuration object
+    (``epix10ka_config_bytes``, whose quadrant layout is restated, not verified).  Raises RuntimeError with
+    what was tried when nothing yields an array of the detector's shape."""
+    tried = []
+    want = tuple(shape)
+
+    def fit(a):
+        a = np.asarray(a)
+        if a.shape == want[1:]:
+            a = a[None]
+        if a.shape != want:
+            raise ValueError(f"shape {a.shape}, expected {want}")
+        return (a & 0x1C).astype(np.uint8)
+
+    try:
+        from Detector import UtilsEpix10ka as ue
+    except ImportError as e:
+        ue = None
+        tried.append(f"import Detector.UtilsEpix10ka: {e}")
+    cob = None
+    if ue is not None:
+        getter = getattr(ue, "get_epix10ka_any_config_object", None)
+        if getter is not None:
+            try:
+                cob = getter(env, source)
+            except Exception as e:                                        # noqa: BLE001
+                tried.append(f"get_epix10ka_any_config_object: {e!r}")
+        fn = getattr(ue, "cbits_config_epix10ka_any", None)
+        if fn is not None:
+            for arg, label in ((cob, "config object"), (det, "detector")):
+                if arg is None:
+                    continue
+                try:
+                    return fit(fn(arg))
+                except Exception as e:                                    # noqa: BLE001
+                    tried.append(f"cbits_config_epix10ka_any({label}): {e!r}")
+    if cob is not None:
+        try:
+            elems = [cob.elemCfg(i) for i in range(cob.numberOfElements())] if hasattr(cob, "numberOfElements") else [cob]
+            segs = [epix10ka_config_bytes(np.asarray(e.asicPixelConfigArray()), [e.asics(i).trbit() for i in range(4)]) for e in elems]
+            return fit(np.stack(segs))
+        except Exception as e:                                            # noqa: BLE001
+            tried.append(f"config object -> epix10ka_config_bytes: {e!r}")
+    raise RuntimeError("could not build the epix10ka per-pixel config bytes from psana (pass epix10ka_cfg=...); tried: " + "; ".join(tried))
+
+
+class PsanaSource:
+    """psana-backed source (LCLS-I psana1) with the shape of ``PsanaWrapperSmd`` as the reference uses it
+    (ref: producer.py:81,88,150-154), but yielding RAW frames and the run's constants.  Needs ``import psana``.
+
+    ``calib_mask`` is the mask ``det.calib`` itself multiplies by (psana: the pixel-status mask, ``mbits=1``) --
+    NOT the producer's bad-pixel mask, which the reference applies afterwards and only under
+    ``--uses_bad_pixel_mask`` (ref: producer.py:81,92-93); that one is ``create_bad_pixel_mask()`` and goes to
+    ``set_keep_mask``.  "status" | "total" | "none", or an array.
+    ``common_mode``: cmpars override (``--common_mode``); None = the run's ``common_mode`` calibration constant.
+    ``epix10ka_cfg``: per-pixel config bytes override; None = read from the detector's configuration (above).
+    """
+
+    def __init__(self, exp, run, detector_name, rank=0, size=1, epix10ka_cfg=None, common_mode=None, calib_mask="status"):
         import psana                                                      # noqa: F401  (not available offline)
         self._psana = psana
         self.exp, self.run, self.detector_name = exp, int(run), detector_name
         self.rank, self.size = rank, size
         self.ds = psana.MPIDataSource(f"exp={exp}:run={self.run}:smd")
         self.det = psana.Detector(detector_name)
-        self.ebeam = psana.Detector("EBeam")
+        try:
+            self.ebeam = psana.Detector("EBeam")
+        except Exception:                                                 # noqa: BLE001  (runs without an EBeam record)
+            self.ebeam = None
         self.spec = syn.detector_spec(detector_name)
         self._cfg = epix10ka_cfg
+        self._cmpars = common_mode
+        self._calib_mask = calib_mask
+
+    def _mask_for_calib(self, shape):
+        m = self._calib_mask
+        if m is None or (isinstance(m, str) and m == "none"):
+            return None
+        if isinstance(m, str):
+            if m == "status":
+                arr = self.det.mask(self.run, calib=False, status=True, edges=False, central=False, unbond=False, unbondnbrs=False)
+            elif m == "total":
+                arr = self.det.mask(self.run, calib=True, status=True, edges=True, central=True, unbond=True, unbondnbrs=True)
+            else:
+                raise ValueError(f"calib_mask = {m!r}")
+        else:
+            arr = m
+        arr = np.asarray(arr)
+        return (arr.reshape(shape) != 0).astype(np.uint8)
 
     def constants(self):
         r = self.run
-        out = {"peds": np.asarray(self.det.pedestals(r), dtype=np.float32),
-               "gain": np.asarray(self.det.gain(r), dtype=np.float32),
-               "mask": np.asarray(self.create_bad_pixel_mask(), dtype=np.uint8)}
+        peds = np.asarray(self.det.pedestals(r), dtype=np.float32)
+        if peds.ndim == 3:                                                # single-segment detectors come without the segment axis
+            peds = peds[:, None]
+        self.spec = self.spec.with_nseg(peds.shape[1])
+        full = (self.spec.nmodes,) + self.spec.shape
+        out = {"peds": peds.reshape(full)}
+        gain = self.det.gain(r)
+        out["gain"] = np.ones(full, dtype=np.float32) if gain is None else np.asarray(gain, dtype=np.float32).reshape(full)
+        mask = self._mask_for_calib(self.spec.shape)
+        if mask is not None:
+            out["mask"] = mask
         if self.spec.kind == "jungfrau":
             offs = self.det.offset(r)
             if offs is not None:
-                out["offs"] = np.asarray(offs, dtype=np.float32)
+                out["offs"] = np.asarray(offs, dtype=np.float32).reshape(full)
         else:
-            if self._cfg is None:
-                raise RuntimeError("epix10ka needs the per-pixel config bytes (pixel gain bits | trbit << 4); "
-                                   "pass epix10ka_cfg built from the detector's configuration object")
-            out["cfg"] = np.asarray(self._cfg, dtype=np.uint8)
-        self.spec = self.spec.with_nseg(out["peds"].shape[1])
+            cfg = self._cfg
+            if cfg is None:
+                cfg = _epix10ka_cfg_from_psana(self.det, getattr(self.ds, "env", lambda: None)(), getattr(self.det, "source", None), self.spec.shape)
+            out["cfg"] = np.asarray(cfg, dtype=np.uint8).reshape(self.spec.shape)
         return out
 
     def common_mode(self):
+        if self._cmpars is not None:
+            return tuple(self._cmpars)
         cm = self.det.common_mode(self.run)
-        return None if cm is None else tuple(cm)
+        if cm is None:
+            return None
+        cm = [float(v) for v in np.asarray(cm).ravel()]
+        if len(cm) < 3 or int(cm[0]) == 0:
+            return None
+        return (int(cm[0]), int(cm[1]), float(cm[2])) + ((int(cm[3]),) if len(cm) > 3 else ())
 
     def geometry(self):
-        return (np.asarray(self.det.indexes_x(self.run), dtype=np.int32),
-                np.asarray(self.det.indexes_y(self.run), dtype=np.int32))
+        return (np.asarray(self.det.indexes_x(self.run), dtype=np.int32).reshape(self.spec.shape),
+                np.asarray(self.det.indexes_y(self.run), dtype=np.int32).reshape(self.spec.shape))
 
     def create_bad_pixel_mask(self):
-        return self.det.mask(self.run, calib=True, status=True, edges=True, central=True, unbond=True, unbondnbrs=True)
+        """``PsanaWrapperSmd.create_bad_pixel_mask`` (ref: producer.py:81): 1 = good; the producer's keep mask."""
+        m = self.det.mask(self.run, calib=True, status=True, edges=True, central=True, unbond=True, unbondnbrs=True)
+        return np.asarray(m).reshape((-1,) + self.spec.shape[1:])
 
     def iter_raw_events(self):
         for evt in self.ds.events():                                      # MPIDataSource shards nevent % size == rank
             raw = self.det.raw(evt)
-            if raw is None:
+            if raw is None:                                               # detector missing from this event
                 continue
-            eb = self.ebeam.get(evt)
-            yield np.asarray(raw, dtype=np.uint16), (eb.ebeamPhotonEnergy() if eb is not None else None)
+            energy = None
+            if self.ebeam is not None:
+                eb = self.ebeam.get(evt)
+                if eb is not None:
+                    energy = eb.ebeamPhotonEnergy()
+            yield np.asarray(raw).astype(np.uint16, copy=False).reshape((-1,) + self.spec.shape[1:]), energy

@@ -53,6 +53,11 @@ def parse_arguments(argv=None):
                         help="Event source: seeded synthetic frames (default) or a real psana run")
     parser.add_argument("--num_events", type=int, default=1024, help="Synthetic source: events in the run (all ranks)")
     parser.add_argument("--common_mode", type=str, default=None, help="cmpars as 'alg,mode,cormax[,npix_min]'")
+    parser.add_argument("--calib_mask", type=str, default="status", choices=["status", "total", "none"],
+                        help="psana source: the mask det.calib itself multiplies by (psana default: pixel status)")
+    parser.add_argument("--epix10ka_cfg_path", type=str, default=None,
+                        help="psana source: npy of per-pixel epix10ka config bytes (bits 3,2 pixel gain config | bit 4 trbit), "
+                             "instead of reading them from the detector's configuration")
     parser.add_argument("--reliable_sentinels", action="store_true",
                         help="Retry the end-of-stream sentinels with the put back-off instead of dropping them when the queue is full "
                              "(the reference drops them: producer.py:125 ignores put's result)")
@@ -357,7 +362,9 @@ def make_source(args, world):
         cm = (int(p[0]), int(p[1]), float(p[2])) + ((int(p[3]),) if len(p) > 3 else ())
     if args.source == "psana":
         from .event_source import PsanaSource
-        return PsanaSource(exp=args.exp, run=args.run, detector_name=args.detector_name, rank=world.rank, size=world.size)
+        cfg = np.load(args.epix10ka_cfg_path) if args.epix10ka_cfg_path else None
+        return PsanaSource(exp=args.exp, run=args.run, detector_name=args.detector_name, rank=world.rank, size=world.size,
+                           epix10ka_cfg=cfg, common_mode=cm, calib_mask=args.calib_mask)
     return SyntheticSource(exp=args.exp, run=args.run, detector_name=args.detector_name, rank=world.rank, size=world.size,
                            num_events=args.num_events, common_mode=cm)
 
