@@ -25,7 +25,7 @@ dev = int(sys.argv[1]); torch.cuda.set_device(dev)
 t_deadline = time.time() + 120
 while True:
     try:
-        rd = DataReader(queue_name="stream", ray_namespace="bench", device=dev); rd.connect(); break
+        rd = DataReader(queue_name="stream", ray_namespace="bench", device=dev, zero_copy=True); rd.connect(); break
     except ValueError:
         if time.time() > t_deadline: raise
         time.sleep(0.05)

@@ -86,7 +86,9 @@ int psr_set_common_mode(psr_ctx* ctx, int mode_bits, float cormax, int npix_min,
 
 /* Geometry for PSR_OUT_IMAGE: per-pixel image indices as det.indexes_x/y give them
  * (PSCalib/GeometryAccess.py::img_from_pixel_arrays).  Builds the inverse gather map with
- * last-writer-wins for duplicate targets; image shape = (max(iX)+1, max(iY)+1). */
+ * last-writer-wins for duplicate targets; image shape = (max(iX)+1, max(iY)+1).
+ * A new geometry is a new image: an installed PSR_OUT_IMAGE keep mask is CLEARED by this call (its
+ * element count belongs to the old image shape) -- install it again afterwards. */
 int psr_set_geometry(psr_ctx* ctx, const int32_t* h_iX, const int32_t* h_iY);
 int psr_image_shape(const psr_ctx* ctx, int* H, int* W);
 
@@ -95,9 +97,11 @@ int psr_image_shape(const psr_ctx* ctx, int* H, int* W);
  * output frame of `out_kind`.  NULL clears. */
 int psr_set_keep_mask(psr_ctx* ctx, const uint8_t* h_keep, size_t n, int out_kind);
 
-/* Pre-size the context's scratch (image mode with a common-mode word other than 4 goes through a
- * calibrated-frame scratch of max_frames; bank medians alone -- word 4 -- and no common mode write the
- * image directly) so that psr_calib_batch never allocates. */
+/* Size the context's scratch.  PSR_OUT_IMAGE with a common-mode word other than 4 goes through a
+ * calibrated-frame scratch of max_frames (bank medians alone -- word 4 -- and no common mode write
+ * the image directly and need none).  The hot call never allocates: psr_calib_batch returns
+ * PSR_E_INVALID if such a batch is larger than what was reserved.  psr_calib_batch_host sizes the
+ * scratch for its chunks itself, together with its staging ring, on its first call. */
 int psr_reserve(psr_ctx* ctx, int max_frames);
 
 /* Tuning knobs that change speed, never results.  "frames_per_block": frames one CTA of the
@@ -118,17 +122,22 @@ int psr_calib_batch(psr_ctx* ctx, const uint16_t* d_raw, int nframes, float* d_o
  * GPU whose memory another job (typically a PyTorch caching allocator) has already claimed, where
  * cudaMalloc simply fails; and a latency-critical acquisition loop that must never take the
  * device-wide synchronisation that cudaMalloc / cudaFree imply.  psr_calib_batch(PSR_OUT_IMAGE) with
- * common mode on parks the calibrated frames in a scratch buffer the context allocates (psr_reserve
- * or first use); this variant runs the same two kernels but parks them in a fixed array that is part
- * of the library image, PSR_NOALLOC_SCRATCH_BYTES long, which every GPU that loads the library
- * carries until the process exits.  It calls no cudaMalloc, cudaFree or any other allocating routine.
- *   - limit: nframes * nseg*rows*cols * 4 bytes must fit the array -- 3 frames of epix10k2M, 1 frame
+ * a row / column common-mode word parks the calibrated frames in a scratch buffer the context
+ * allocates (psr_reserve); this variant runs the same two kernels but parks them in a fixed array
+ * that is part of the library image, PSR_NOALLOC_SCRATCH_BYTES long, which every GPU that loads the
+ * library carries until the process exits.  It calls no cudaMalloc, cudaFree or any other allocating
+ * routine.  (With common mode off, or bank medians only, the kernels write the image directly and
+ * the array is not touched; the limit below is the call's contract all the same.)
+ *   - limit: nframes * nseg*rows*cols * 4 bytes must fit the array -- 3 frames of epix10k2M, 2 frames
  *     of Jungfrau 4M per call; larger requests are rejected with PSR_E_INVALID and a message naming
  *     the limit.  Loop over the batch in slices.
  *   - d_raw and d_img are the caller's, exactly as for psr_calib_batch; results are identical to it,
  *     with common mode on or off.
- *   - the first call on each device looks the array's device address up once (with that device
- *     current); make that first call before starting any stream capture.
+ *   - set-up happens in psr_create, not here: with the context's device current it looks the array's
+ *     device address up once per device, which is also the moment the driver loads this library's
+ *     device code -- the 32 MiB array included -- onto that GPU.  Create the context at start-up,
+ *     before other jobs claim the GPU's memory and before any stream capture; the calls themselves
+ *     then neither load nor allocate anything.
  *   - the array is shared by every call and every context on the device and keeps the previous
  *     call's contents; nothing in it has to start at zero, because each call overwrites the part it
  *     later reads.  Two calls whose kernels overlap on the GPU (different streams, or different
@@ -145,7 +154,21 @@ int psr_decode_gain_modes(psr_ctx* ctx, const uint16_t* d_raw, int nframes, uint
  * NULL) and/or h_out (host, may be NULL).  Replaces one producer loop iteration block
  * (ref: producer.py:88-101) for `nframes` events.  Synchronous: returns when h_out/d_out are final. */
 int psr_calib_batch_host(psr_ctx* ctx, const uint16_t* h_raw, int nframes, float* h_out, float* d_out, int out_kind);
-int psr_set_host_chunk(psr_ctx* ctx, int chunk_frames, int depth);   /* staging ring geometry; default 8 x 3 */
+
+/* The same, asynchronously: _begin queues the copies and kernels of the batch on the context's own
+ * streams and returns; `done_event` (nullable; a cudaEvent_t as void*, e.g. from
+ * psr_ipc_event_create) is recorded where the batch is final, so a producer can publish the batch's
+ * descriptor at once -- ref: producer.py:99-103 puts only after the data exists -- and a consumer in
+ * another process waits on the event in its own stream (psr_event_wait) instead of the producer
+ * blocking.  Calls may overlap: a second _begin may be issued while the first is in flight (the
+ * staging slots are handed on in order).  _wait(PSR_WAIT_INPUT) returns when every h_raw passed so
+ * far has been read (the host buffer may be refilled); _wait(PSR_WAIT_ALL) when everything is done. */
+#define PSR_WAIT_INPUT 0
+#define PSR_WAIT_ALL   1
+int psr_calib_batch_host_begin(psr_ctx* ctx, const uint16_t* h_raw, int nframes, float* h_out, float* d_out, int out_kind, void* done_event);
+int psr_calib_batch_host_wait(psr_ctx* ctx, int what);
+int psr_set_host_chunk(psr_ctx* ctx, int chunk_frames, int depth);   /* staging ring geometry; default 8 x 4; the chunks of a call
+                                                                      * ramp up 1, 1, 2, 4 ... to chunk_frames so the pipeline fills fast */
 
 /* memory helpers for callers without their own CUDA allocator */
 int psr_host_alloc(void** h_ptr, size_t bytes);          /* pinned */

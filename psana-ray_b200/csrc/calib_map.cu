@@ -647,8 +647,7 @@ cudaError_t psr_launch_calib_map(const PsrDev& c, const uint16_t* d_raw, int nfr
         const float4 *a0 = reinterpret_cast<const float4*>(c.ped0), *a1 = reinterpret_cast<const float4*>(c.gf0);
         const float4 *a2 = reinterpret_cast<const float4*>(c.ped1), *a3 = reinterpret_cast<const float4*>(c.gf1);
         if (persist) {
-            static int nres = 0;
-            if (!nres) nres = resident_ctas(epix_calib_map_kernel<true>, MAP_THREADS);
+            const int nres = resident_ctas(epix_calib_map_kernel<true>, MAP_THREADS);       // per launch: the current device's, no shared state
             const long long total = (long long)ntiles * nframes;
             const int grid = (int)(total < nres ? total : nres);
             epix_calib_map_kernel<true><<<grid, MAP_THREADS, 0, st>>>(raw, out, a0, a1, a2, a3, fl, ngroups, nframes, fpb, ntiles);
@@ -662,8 +661,7 @@ cudaError_t psr_launch_calib_map(const PsrDev& c, const uint16_t* d_raw, int nfr
         const long long total = (long long)ntiles * nframes;
 #define PSR_JF_LAUNCH(OFFS)                                                                                          \
         if (persist) {                                                                                               \
-            static int nres = 0;                                                                                     \
-            if (!nres) nres = resident_ctas(jf_calib_map_kernel<OFFS, true>, JF_THREADS);                          \
+            const int nres = resident_ctas(jf_calib_map_kernel<OFFS, true>, JF_THREADS);                            \
             const int grid = (int)(total < nres ? total : nres);                                                     \
             jf_calib_map_kernel<OFFS, true><<<grid, JF_THREADS, 0, st>>>(raw, out, p, o, g, fl, ngroups, nframes, fpb, ntiles); \
         } else {                                                                                                     \

@@ -65,11 +65,12 @@ inline int epix_mode_of_cbits(unsigned cb) {
 inline float gfac_of(float g) { return g != 0.0f ? 1.0f / g : 0.0f; }   // divide_protected(1, gain)
 
 struct HostPipe {
-    int chunk = 8, depth = 3;
+    int chunk = 8, depth = 4;
     cudaStream_t s_in = nullptr, s_comp = nullptr, s_out = nullptr;
     std::vector<uint16_t*> d_raw; std::vector<float*> d_out;
     std::vector<cudaEvent_t> ev_in, ev_comp, ev_out;
     size_t raw_elems = 0, out_elems = 0;      // per slot
+    long long seq = 0;                        // chunks issued so far (across calls: a call may still be in flight when the next begins)
 };
 
 }  // namespace
@@ -92,7 +93,7 @@ struct psr_ctx {
     float* d_scratch = nullptr; size_t scratch_elems = 0;
     cudaStream_t s_gap = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr;    // gap fill runs beside the scatter kernels
     int image_gather = 0;          // 1: raw -> image through the output-driven gather kernel instead of the scatter kernel
-    int frames_per_block = 0;      // 0 = auto: persistent balanced schedule; > 0 forces the (tile, frame chunk) grid
+    int frames_per_block = 0;      // map kernels: 0 = whole batch (<= 64 frames) per CTA on a plain grid, > 0 = that many frames per CTA, < 0 = persistent balanced schedule
     HostPipe pipe;
 };
 
@@ -150,7 +151,7 @@ void free_pipe(HostPipe& p) {
     for (auto e : p.ev_comp) if (e) cudaEventDestroy(e);
     for (auto e : p.ev_out) if (e) cudaEventDestroy(e);
     p.d_raw.clear(); p.d_out.clear(); p.ev_in.clear(); p.ev_comp.clear(); p.ev_out.clear();
-    p.raw_elems = p.out_elems = 0;
+    p.raw_elems = p.out_elems = 0; p.seq = 0;
 }
 
 size_t out_frame_elems(const psr_ctx* c, int out_kind) {
@@ -169,11 +170,6 @@ int ensure_scratch(psr_ctx* c, size_t elems) {
 // other pixels, so the two need no order between them, only both after what `st` held before and both before what follows.
 int gap_fill_fork(psr_ctx* c, int nframes, float* d_img, cudaStream_t st) {
     if (c->dev.ngaps <= 0) return PSR_OK;
-    if (!c->s_gap) {
-        PSR_CUDA(cudaStreamCreateWithFlags(&c->s_gap, cudaStreamNonBlocking));
-        PSR_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
-        PSR_CUDA(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
-    }
     PSR_CUDA(cudaEventRecord(c->ev_fork, st));
     PSR_CUDA(cudaStreamWaitEvent(c->s_gap, c->ev_fork, 0));
     PSR_CUDA(psr_launch_image_gap_fill(c->dev, nframes, d_img, c->s_gap));
@@ -188,7 +184,7 @@ int gap_fill_join(psr_ctx* c, cudaStream_t st) {
 
 int launch_batch(psr_ctx* c, const uint16_t* d_raw, int nframes, float* d_out, int out_kind, cudaStream_t st) {
     const PsrDev& d = c->dev;
-    const int fpb = c->frames_per_block;      // 0 = persistent balanced schedule (map kernels); image gather: whole batch per CTA
+    const int fpb = c->frames_per_block;      // see psr_ctx::frames_per_block
     if (out_kind == PSR_OUT_CALIB) {
         if (d.cm_mode == 0) PSR_CUDA(psr_launch_calib_map(d, d_raw, nframes, d_out, fpb, st));
         else                PSR_CUDA(psr_launch_common_mode(d, d_raw, nframes, d_out, st));
@@ -210,8 +206,10 @@ int launch_batch(psr_ctx* c, const uint16_t* d_raw, int nframes, float* d_out, i
             rc = gap_fill_join(c, st);
             if (rc != PSR_OK) return rc;
         } else {
-            int rc = ensure_scratch(c, (size_t)nframes * d.npix);
-            if (rc != PSR_OK) return rc;
+            // no hidden allocation on the hot call: the scratch of this two-pass path is sized by psr_reserve
+            if (c->scratch_elems < (size_t)nframes * d.npix)
+                return fail(PSR_E_INVALID, "image output with common-mode word %d goes through a calibrated scratch of %d frames: "
+                            "call psr_reserve(ctx, max_frames) once before the first batch", d.cm_mode, nframes);
             // the calib-layout keep mask does not apply to images (ref: producer.py:92-97 masks the 2-D image)
             PsrDev t = d; t.ignore_keep = 1;
             PSR_CUDA(psr_launch_common_mode(t, d_raw, nframes, c->d_scratch, st));
@@ -272,6 +270,21 @@ int psr_create(psr_ctx** out, int det_kind, int nseg, int rows, int cols, int de
     c->elig_mask = det_kind == PSR_DET_EPIX10KA ? 0x1Bu : 0x3u;
     c->dev.elig_mask = c->elig_mask;
     if (const char* e = getenv("PSR_FRAMES_PER_BLOCK")) { int v = atoi(e); if (v > 0) c->frames_per_block = v; }
+    // everything a hot call would otherwise create lazily: the side stream and events of the gap fill, and the device address
+    // of psr_calib_image_noalloc's built-in scratch (the lookup loads this library's device code -- and with it the array --
+    // onto the device, so it happens here, at start-up, not inside a call that promised not to allocate)
+    cudaError_t e1 = cudaStreamCreateWithFlags(&c->s_gap, cudaStreamNonBlocking);
+    if (e1 == cudaSuccess) e1 = cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
+    if (e1 == cudaSuccess) e1 = cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming);
+    if (e1 == cudaSuccess && device < NOALLOC_MAX_DEVICES) {
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_ptr[device]) {
+            void* p = nullptr;
+            e1 = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+            if (e1 == cudaSuccess) g_noalloc_ptr[device] = static_cast<float*>(p);
+        }
+    }
+    if (e1 != cudaSuccess) { psr_destroy(c); return fail(PSR_E_CUDA, "psr_create: %s", cudaGetErrorString(e1)); }
     *out = c;
     return PSR_OK;
 }
@@ -523,17 +536,22 @@ int psr_calib_image_noalloc(psr_ctx* c, const uint16_t* d_raw, int nframes, floa
     DeviceGuard g(c->device);
     if (!g.ok) return fail(PSR_E_CUDA, "cudaSetDevice(%d) failed", c->device);
     float* scratch = nullptr;
-    {   // once per device, with that device current: the symbol's address on THIS device
+    {   // the symbol's address on THIS device, looked up once per device by psr_create with that device current
         std::lock_guard<std::mutex> lk(g_noalloc_mu);
-        if (!g_noalloc_ptr[c->device]) {
-            void* p = nullptr;
-            PSR_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
-            g_noalloc_ptr[c->device] = static_cast<float*>(p);
-        }
         scratch = g_noalloc_ptr[c->device];
     }
+    if (!scratch) return fail(PSR_E_CUDA, "psr_calib_image_noalloc: no scratch address for device %d", c->device);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     PsrDev t = c->dev; t.ignore_keep = 1;       // image mode: producer masks act on the 2-D image only
+    if (t.fwd != nullptr && (t.cm_mode == 0 || t.cm_mode == 4)) {
+        // no common mode, or bank medians only: the kernels that write each pixel straight to its place in the image
+        // need no scratch at all (the gap fill's side stream and events exist since psr_create)
+        rc = gap_fill_fork(c, nframes, d_img, st);
+        if (rc != PSR_OK) return rc;
+        if (t.cm_mode == 0) PSR_CUDA(psr_launch_image_scatter(c->dev, d_raw, nframes, d_img, c->frames_per_block, st));
+        else PSR_CUDA(psr_launch_common_mode_image(t, d_raw, nframes, d_img, st));
+        return gap_fill_join(c, st);
+    }
     // pass 1 writes every pixel of frames [0, nframes) of the scratch, pass 2 reads exactly those: stale
     // contents from an earlier call are never seen, so nothing is cleared
     PSR_CUDA(psr_launch_common_mode(t, d_raw, nframes, scratch, st));
@@ -557,12 +575,11 @@ int psr_set_host_chunk(psr_ctx* c, int chunk_frames, int depth) {
     return PSR_OK;
 }
 
-int psr_calib_batch_host(psr_ctx* c, const uint16_t* h_raw, int nframes, float* h_out, float* d_out, int out_kind) {
+int psr_calib_batch_host_begin(psr_ctx* c, const uint16_t* h_raw, int nframes, float* h_out, float* d_out, int out_kind, void* done_event) {
     if (!h_out && !d_out) return fail(PSR_E_INVALID, "need h_out and/or d_out");
     int rc = check_batch_args(c, h_raw, nframes, h_out ? (const void*)h_out : (const void*)d_out, out_kind);
     if (rc != PSR_OK) return rc;
     if (d_out && ((uintptr_t)d_out & 15u)) return fail(PSR_E_INVALID, "d_out must be 16-byte aligned");
-    if (nframes == 0) return PSR_OK;
     DeviceGuard g(c->device);
     HostPipe& p = c->pipe;
     const size_t npix = (size_t)c->dev.npix, oelems = out_frame_elems(c, out_kind);
@@ -574,6 +591,8 @@ int psr_calib_batch_host(psr_ctx* c, const uint16_t* h_raw, int nframes, float* 
     const bool need_out_slots = (d_out == nullptr);
     if (p.d_raw.empty() || p.raw_elems != (size_t)p.chunk * npix ||
         (need_out_slots && (p.d_out.empty() || p.out_elems < (size_t)p.chunk * oelems))) {
+        // (re)building the ring: nothing of an earlier call may still be using the old one
+        if (p.s_in) { cudaStreamSynchronize(p.s_in); cudaStreamSynchronize(p.s_comp); cudaStreamSynchronize(p.s_out); }
         free_pipe(p);
         p.raw_elems = (size_t)p.chunk * npix;
         for (int i = 0; i < p.depth; ++i) {
@@ -588,13 +607,20 @@ int psr_calib_batch_host(psr_ctx* c, const uint16_t* h_raw, int nframes, float* 
             for (int i = 0; i < p.depth; ++i) { float* o = nullptr; PSR_CUDA(cudaMalloc(&o, p.out_elems * sizeof(float))); p.d_out.push_back(o); }
         }
     }
-    if (out_kind == PSR_OUT_IMAGE && c->dev.cm_mode != 0) { rc = ensure_scratch(c, (size_t)p.chunk * npix); if (rc != PSR_OK) return rc; }
+    if (out_kind == PSR_OUT_IMAGE && c->dev.cm_mode != 0 && c->dev.cm_mode != 4) { rc = ensure_scratch(c, (size_t)p.chunk * npix); if (rc != PSR_OK) return rc; }
 
-    int it = 0;
-    for (int f0 = 0; f0 < nframes; f0 += p.chunk, ++it) {
-        const int nf = (nframes - f0 < p.chunk) ? nframes - f0 : p.chunk;
-        const int s = it % p.depth;
-        if (it >= p.depth) {
+    // Chunk schedule: the copy in one direction is the bottleneck (H2D when the batch stays on the GPU, D2H when it is
+    // copied back), and what the pipeline adds on top is its fill -- the first chunk's H2D + kernel before the first D2H
+    // can start -- and its drain.  So the chunks ramp up from one frame (1, 1, 2, 4, ... up to the configured size).
+    // Slots are numbered by a counter that runs on across calls, so a call that begins while the previous one is still
+    // in flight waits for exactly the slots that one has not finished with.
+    int f0 = 0, ramp = 1, it = 0;
+    while (f0 < nframes) {
+        int nf = ramp < p.chunk ? ramp : p.chunk;
+        if (it >= 1 && ramp < p.chunk) ramp *= 2;
+        if (nf > nframes - f0) nf = nframes - f0;
+        const int s = (int)(p.seq % p.depth);
+        if (p.seq >= p.depth) {
             PSR_CUDA(cudaStreamWaitEvent(p.s_in, p.ev_comp[s], 0));                 // raw slot consumed
             if (need_out_slots) PSR_CUDA(cudaStreamWaitEvent(p.s_comp, p.ev_out[s], 0));   // out slot drained
         }
@@ -613,9 +639,36 @@ int psr_calib_batch_host(psr_ctx* c, const uint16_t* h_raw, int nframes, float* 
             PSR_CUDA(cudaMemcpyAsync(h_out + (size_t)f0 * oelems, o, (size_t)nf * oelems * sizeof(float), cudaMemcpyDeviceToHost, p.s_out));
             PSR_CUDA(cudaEventRecord(p.ev_out[s], p.s_out));
         }
+        f0 += nf; ++it; ++p.seq;
     }
-    PSR_CUDA(cudaStreamSynchronize(p.s_comp));
-    if (h_out) PSR_CUDA(cudaStreamSynchronize(p.s_out));
+    if (done_event) {
+        // the batch is final once the compute stream (d_out) and, with h_out, the copy-out stream are: record on the
+        // one that finishes last, after making it wait for the other
+        cudaStream_t last = p.s_comp;
+        if (h_out) { last = p.s_out; if (nframes > 0) PSR_CUDA(cudaStreamWaitEvent(p.s_out, p.ev_comp[(int)((p.seq - 1) % p.depth)], 0)); }
+        PSR_CUDA(cudaEventRecord(static_cast<cudaEvent_t>(done_event), last));
+    }
+    return PSR_OK;
+}
+
+int psr_calib_batch_host_wait(psr_ctx* c, int what) {
+    if (!c) return fail(PSR_E_INVALID, "null context");
+    if (what != PSR_WAIT_INPUT && what != PSR_WAIT_ALL) return fail(PSR_E_INVALID, "what = %d", what);
+    DeviceGuard g(c->device);
+    HostPipe& p = c->pipe;
+    if (!p.s_in) return PSR_OK;
+    PSR_CUDA(cudaStreamSynchronize(p.s_in));                     // every H2D copy issued so far has read its host source
+    if (what == PSR_WAIT_ALL) { PSR_CUDA(cudaStreamSynchronize(p.s_comp)); PSR_CUDA(cudaStreamSynchronize(p.s_out)); }
+    return PSR_OK;
+}
+
+int psr_calib_batch_host(psr_ctx* c, const uint16_t* h_raw, int nframes, float* h_out, float* d_out, int out_kind) {
+    int rc = psr_calib_batch_host_begin(c, h_raw, nframes, h_out, d_out, out_kind, nullptr);
+    if (rc != PSR_OK) return rc;
+    if (nframes == 0) return PSR_OK;
+    DeviceGuard g(c->device);
+    PSR_CUDA(cudaStreamSynchronize(c->pipe.s_comp));
+    if (h_out) PSR_CUDA(cudaStreamSynchronize(c->pipe.s_out));
     return PSR_OK;
 }
 

@@ -9,6 +9,7 @@ import ctypes as C
 import os
 
 PSR_OK = 0
+PSR_WAIT_INPUT, PSR_WAIT_ALL = 0, 1
 PSR_DET_EPIX10KA, PSR_DET_JUNGFRAU = 0, 1
 PSR_OUT_CALIB, PSR_OUT_IMAGE = 0, 1
 PSR_CM_ROWS, PSR_CM_COLS, PSR_CM_BANKS = 1, 2, 4
@@ -51,6 +52,8 @@ SIGNATURES = {
     "psr_calib_image_noalloc": (_i, [_vp, _vp, _i, _vp, _vp]),
     "psr_decode_gain_modes": (_i, [_vp, _vp, _i, _vp, _vp]),
     "psr_calib_batch_host": (_i, [_vp, _vp, _i, _vp, _vp, _i]),
+    "psr_calib_batch_host_begin": (_i, [_vp, _vp, _i, _vp, _vp, _i, _vp]),
+    "psr_calib_batch_host_wait": (_i, [_vp, _i]),
     "psr_set_host_chunk": (_i, [_vp, _i, _i]),
     "psr_host_alloc": (_i, [_pvp, _sz]),
     "psr_host_free": (_i, [_vp]),

@@ -116,7 +116,7 @@ class GpuSlabs:
             sleep(min(2.0, 0.001 * (2 ** waits)))
             waits = min(waits + 1, 11)
         i, slab, lease = got
-        return slab[:shape[0]], (lambda: self.ring.ref(i, shape[0])), lease
+        return slab[:shape[0]], (lambda: self.ring.ref(i, shape[0], with_event=False)), lease      # published only once final (see run_receiver)
 
     def close(self):
         if self.ring is not None:
@@ -199,7 +199,7 @@ def main(argv=None):
         dist.init_process_group("gloo", rank=rank, world_size=2)
     try:
         if a.role == "send":
-            reader = DataReader(address=a.ray_address, queue_name=a.queue_name, ray_namespace=a.ray_namespace, device=device)
+            reader = DataReader(address=a.ray_address, queue_name=a.queue_name, ray_namespace=a.ray_namespace, device=device, zero_copy=True)   # the batch goes straight onto the wire
             deadline = time.time() + a.connect_timeout
             while True:
                 try:

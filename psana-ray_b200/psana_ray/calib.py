@@ -39,6 +39,7 @@ class GpuCalibrator:
         self._ctx = ctx
         self.image_shape = None
         self.cm_mode = 0
+        self._reserved = 0
 
     # -- per-run set-up ---------------------------------------------------------------------------
     def set_constants(self, peds, gain=None, offs=None, cfg=None, mask=None):
@@ -81,7 +82,10 @@ class GpuCalibrator:
         N.check(self._lib.psr_set_keep_mask(self._ctx, _np_ptr(k), k.size, kind))
 
     def reserve(self, max_frames: int):
+        """Sizes the scratch that image output with a row / column common-mode word goes through.  ``calib()`` grows it
+        on demand (an allocation on that call); reserve the largest batch up front to keep the hot call allocation-free."""
         N.check(self._lib.psr_reserve(self._ctx, int(max_frames)))
+        self._reserved = max(self._reserved, int(max_frames))
 
     def set_option(self, name: str, value: int):
         N.check(self._lib.psr_set_option(self._ctx, name.encode(), int(value)))
@@ -113,6 +117,8 @@ class GpuCalibrator:
         elif tuple(out.shape) != shape or out.dtype != torch.float32 or not out.is_contiguous() or out.device != raw.device:
             raise ValueError(f"out must be a contiguous float32 CUDA tensor of shape {shape}")
         st = stream if stream is not None else torch.cuda.current_stream(raw.device).cuda_stream
+        if image and self.cm_mode not in (0, 4) and nframes > self._reserved:
+            self.reserve(nframes)                   # the C ABI refuses to allocate inside the hot call
         N.check(self._lib.psr_calib_batch(self._ctx, raw.data_ptr(), nframes, out.data_ptr(),
                                           N.PSR_OUT_IMAGE if image else N.PSR_OUT_CALIB, st))
         return out
@@ -122,7 +128,7 @@ class GpuCalibrator:
 
         For consumers that share a GPU whose memory is already spoken for, or loops that cannot afford
         the device-wide stall of an allocation.  ``out`` must be supplied by the caller; at most
-        ``PSR_NOALLOC_SCRATCH_BYTES // (4 * npix)`` frames per call (3 for epix10k2M, 1 for Jungfrau 4M).
+        ``PSR_NOALLOC_SCRATCH_BYTES // (4 * npix)`` frames per call (3 for epix10k2M, 2 for Jungfrau 4M).
         Calls on one device share one scratch array: keep them on one stream.
         """
         import torch
@@ -160,7 +166,7 @@ class GpuCalibrator:
             return 2                    # scatter / fused common-mode kernel + the gap-fill kernel beside it
         return 2                        # common mode into scratch + gather
 
-    def calib_host(self, h_raw, h_out=None, d_out=None, image: bool = False):
+    def calib_host(self, h_raw, h_out=None, d_out=None, image: bool = False, begin_only: bool = False, done_event=None):
         """Host-fed form: ``h_raw`` is a NumPy array or CPU tensor (pinned for full speed), ``h_out`` likewise,
         ``d_out`` a CUDA tensor on this calibrator's device.  Shapes, dtypes and contiguity are checked here: the
         C ABI below takes bare pointers."""
@@ -197,8 +203,20 @@ class GpuCalibrator:
         pr, n = ptr_n(h_raw)
         po, _ = ptr_n(h_out)
         pd = None if d_out is None else d_out.data_ptr()
-        N.check(self._lib.psr_calib_batch_host(self._ctx, pr, n, po, pd,
-                                               N.PSR_OUT_IMAGE if image else N.PSR_OUT_CALIB))
+        kind = N.PSR_OUT_IMAGE if image else N.PSR_OUT_CALIB
+        if begin_only:
+            N.check(self._lib.psr_calib_batch_host_begin(self._ctx, pr, n, po, pd, kind, done_event))
+        else:
+            N.check(self._lib.psr_calib_batch_host(self._ctx, pr, n, po, pd, kind))
+
+    def calib_host_begin(self, h_raw, h_out=None, d_out=None, image: bool = False, done_event=None):
+        """Asynchronous ``calib_host``: queues the batch on the library's streams and returns.  ``done_event`` (a raw
+        ``cudaEvent_t`` value, e.g. a slab's inter-process event) is recorded where the batch is final.  The host buffer
+        must stay untouched until ``calib_host_wait(input_only=True)``."""
+        self.calib_host(h_raw, h_out=h_out, d_out=d_out, image=image, begin_only=True, done_event=done_event)
+
+    def calib_host_wait(self, input_only: bool = False):
+        N.check(self._lib.psr_calib_batch_host_wait(self._ctx, N.PSR_WAIT_INPUT if input_only else N.PSR_WAIT_ALL))
 
     def close(self):
         if getattr(self, "_ctx", None):

@@ -6,11 +6,20 @@ raises ``RuntimeError`` when unconnected (:32-33) and ``DataReaderError`` when t
 (:36-37); ``close()`` (:26-29); context manager (:39-44); ``DataReaderError`` (:46-48).
 
 An item is still the reference's ``[rank, idx, data, photon_energy]`` (ref: producer.py:101);
-``data`` is now a CUDA ``torch.Tensor`` view -- ``(segs, rows, cols)`` or ``(1, H, W)`` float32 --
-into the producer's slab, mapped once per slab through CUDA IPC, instead of an ndarray unpickled
+``data`` is now a CUDA ``torch.Tensor`` -- ``(segs, rows, cols)`` or ``(1, H, W)`` float32 -- taken
+from the producer's slab, mapped once per slab through CUDA IPC, instead of an ndarray unpickled
 from the object store.  Producers queue whole batches; ``read()`` de-batches locally, so most calls
 cost no round trip at all.  Additive: ``read_batch()``, ``__iter__`` (stops at the end-of-stream
 sentinel, which ``read()`` cannot tell from an empty queue -- both are ``None`` in the reference).
+
+LIFETIME.  The reference hands every consumer an ndarray it owns.  By default so does this reader:
+``read()`` / ``read_batch()`` / iteration return a device-to-device COPY of the frame(s) (a few
+microseconds on the GPU's own bandwidth), which the caller may keep as long as it likes.  With
+``zero_copy=True`` they return VIEWS into the producer's slab instead: those are valid only until the
+reader moves past their batch -- the next ``read_batch()``, the ``read()`` that crosses into the next
+batch, or ``close()`` -- at which point the slab goes back to its producer and is overwritten.  In
+both modes the reader waits for the work queued on the consumer's stream (the copies, or whatever the
+caller launched on the views) before it returns a slab, so nothing in flight reads a recycled slab.
 """
 import time
 
@@ -19,11 +28,13 @@ from .transport import EventBatch, GpuBatchRef
 
 
 class DataReader:
-    def __init__(self, address='auto', queue_name="shared_queue", ray_namespace='my', device=None):
+    def __init__(self, address='auto', queue_name="shared_queue", ray_namespace='my', device=None, zero_copy=False, premap=True):
         self.address = address
         self.queue_name = queue_name
         self.ray_namespace = ray_namespace
         self.device = device          # CUDA device GPU batches are mapped on; None = current device at first use
+        self.zero_copy = zero_copy    # True: hand out views into the producer's slab (see LIFETIME above)
+        self.premap = premap          # map every registered producer slab at connect(), not on first touch
         self._queue = None
         self._mapper = None
         self._batch = None            # EventBatch being handed out
@@ -39,6 +50,13 @@ class DataReader:
             print(f"Error getting queue actor: {e}")
             self.close()
             raise
+        if self.premap:
+            try:
+                tables = self._queue.list_slabs()
+                if tables:
+                    self._ensure_mapper().premap(tables)
+            except Exception:
+                pass                                  # mapping falls back to first touch
 
     def close(self):
         self._finish_batch()
@@ -78,7 +96,7 @@ class DataReader:
                 item, self._loose = self._loose, None
                 return item
         b, c = self._batch, self._cursor
-        out = [b.rank, b.idx0 + c, self._tensor[c:], list(b.photon_energy[c:])]
+        out = [b.rank, b.idx0 + c, self._own(self._tensor[c:]), list(b.photon_energy[c:])]
         self._cursor = b.count
         return out
 
@@ -94,24 +112,38 @@ class DataReader:
             yield item
 
     # -- internals --------------------------------------------------------------------------------------------
+    def _own(self, t):
+        """What the caller gets: a copy it owns (default), or the view itself (zero_copy)."""
+        if self.zero_copy or not hasattr(t, "clone"):
+            return t
+        return t.clone()
+
     def _finish_batch(self):
-        b = self._batch
+        b, t = self._batch, self._tensor
         self._batch = self._tensor = None
         self._cursor = 0
+        if t is not None and getattr(t, "is_cuda", False):
+            # the copies handed out (or the caller's kernels on the views) are queued on the consumer's stream: they must
+            # have read the slab before its producer may overwrite it
+            import torch
+            torch.cuda.current_stream(t.device).synchronize()
         if b is not None and b.lease is not None and self._queue is not None:
             try:
                 self._queue.release(b.lease)
             except Exception:
                 pass
 
+    def _ensure_mapper(self):
+        if self._mapper is None:
+            import torch
+            from .transport import SlabMapper
+            dev = self.device if self.device is not None else torch.cuda.current_device()
+            self._mapper = SlabMapper(dev)
+        return self._mapper
+
     def _map(self, data):
         if isinstance(data, GpuBatchRef):
-            if self._mapper is None:
-                import torch
-                from .transport import SlabMapper
-                dev = self.device if self.device is not None else torch.cuda.current_device()
-                self._mapper = SlabMapper(dev)
-            return self._mapper.map(data)
+            return self._ensure_mapper().map(data)    # the current stream now waits for the producer's "batch is final" event
         return data
 
     def _fetch(self):
@@ -153,7 +185,7 @@ class DataReader:
                 return True, item
         b, c = self._batch, self._cursor
         self._cursor += 1
-        return True, [b.rank, b.idx0 + c, self._tensor[c], b.photon_energy[c]]
+        return True, [b.rank, b.idx0 + c, self._own(self._tensor[c]), b.photon_energy[c]]
 
 
 class DataReaderError(Exception):

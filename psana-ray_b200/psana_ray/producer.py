@@ -199,11 +199,18 @@ class GpuBatchPipeline:
         self.h_raw = torch.empty((self.batch_size,) + self.spec.shape, dtype=torch.int16).pin_memory()
         self._h_raw_np = self.h_raw.numpy().view(np.uint16)
         self.ring = SlabRing(nslabs, (self.batch_size,) + self.event_shape, device)
+        self._registered = False
 
     def stage(self, k, raw_frame):
         self._h_raw_np[k] = raw_frame
 
     def poll(self, queue):
+        if not self._registered:                      # once: consumers map every slab and event when they connect
+            try:
+                queue.register_slabs(self.ring.table())
+            except Exception:
+                pass
+            self._registered = True
         self.ring.reclaim(queue.poll_released(self.ring.owner))
 
     def process(self, n, queue):
@@ -214,7 +221,10 @@ class GpuBatchPipeline:
             return None
         i, slab, lease = got
         d_out = slab[:n].view((n,) + (self.cal.image_shape if self.image else self.spec.shape))
-        self.cal.calib_host(self.h_raw[:n], d_out=d_out, image=self.image)     # returns when the slab is final
+        # queued, not waited for: the slab's inter-process event is recorded behind the kernels and the descriptor is
+        # published at once; only the staging buffer is waited for, because the next events are staged into it
+        self.cal.calib_host_begin(self.h_raw[:n], d_out=d_out, image=self.image, done_event=self.ring.events[i])
+        self.cal.calib_host_wait(input_only=True)
         return self.ring.ref(i, n), lease
 
     def process_view(self, h_raw_view, queue):
@@ -226,13 +236,19 @@ class GpuBatchPipeline:
             return None
         i, slab, lease = got
         d_out = slab[:n].view((n,) + (self.cal.image_shape if self.image else self.spec.shape))
-        self.cal.calib_host(h_raw_view, d_out=d_out, image=self.image)
+        # the pool the view comes from is read-only, so nothing is waited for here: the next batch's copies queue up
+        # right behind this one's
+        self.cal.calib_host_begin(h_raw_view, d_out=d_out, image=self.image, done_event=self.ring.events[i])
         return self.ring.ref(i, n), lease
 
     def unprocess(self, lease):
         self.ring.give_back(lease)
 
     def close(self):
+        try:
+            self.cal.calib_host_wait()                # nothing of ours may still be writing a slab that is about to be freed
+        except Exception:
+            pass
         self.cal.close()
         self.ring.close()
 
@@ -414,12 +430,18 @@ def main(argv=None):
         logging.error(traceback.format_exc())
         raise
     finally:
-        # keep the slabs alive until consumers have drained what this rank queued
+        # Keep the slabs alive until every lease has come back: a consumer that still holds a batch (or has not yet read
+        # one that sits in the queue) must never find freed memory behind its mapping.  Leases of consumers that died are
+        # returned by the queue server when their connection drops, so this ends; it is cut short only if the queue is
+        # dead, or after PSANA_RAY_DRAIN_S seconds when that is set (unset = wait).
         if pipeline is not None:
-            t0 = time.time()
+            t0, limit, said = time.time(), os.environ.get("PSANA_RAY_DRAIN_S"), 0.0
             try:
-                while pipeline.ring.out and time.time() - t0 < float(os.environ.get("PSANA_RAY_DRAIN_S", "30")):
+                while pipeline.ring.out and (limit is None or time.time() - t0 < float(limit)):
                     pipeline.poll(queue)
+                    if time.time() - t0 - said >= 10.0:
+                        said = time.time() - t0
+                        logging.info(f"Rank {rank}: waiting for {len(pipeline.ring.out)} batch(es) still with consumers or in the queue")
                     time.sleep(0.05)
             except Exception:
                 pass

@@ -12,7 +12,9 @@ Beyond put/get/size the server keeps the bookkeeping the GPU hand-off needs:
   * leases -- a batch item may name the producer slab it lives in; the lease is attached to the
     consumer connection that got it and is released explicitly, or automatically when that
     connection drops (a crashed consumer must not wedge the producer's ring);
-  * a counting barrier, standing in for MPI.COMM_WORLD.Barrier() (ref: producer.py:53,120).
+  * a counting barrier, standing in for MPI.COMM_WORLD.Barrier() (ref: producer.py:53,120);
+  * the producers' slab tables (CUDA-IPC memory and event handles), so that a consumer can map every
+    slab when it connects instead of on first touch inside the stream.
 
     python -m psana_ray.queue_server --path /tmp/psana_ray_0/default/my.sock --maxsize 400
 """
@@ -43,6 +45,7 @@ class QueueServer:
         self.queue = Queue(maxsize)
         self.released = {}          # owner -> [lease, ...] waiting to be polled by the producer
         self.barriers = {}          # tag -> arrivals so far
+        self.slab_tables = {}       # owner -> table of a producer's slab ring (memory + event handles), registered once
         self.nput = self.nget = self.nrefused = 0
         self.running = True
         self.sel = selectors.DefaultSelector()
@@ -97,6 +100,13 @@ class QueueServer:
 
     def op_poll_released(self, conn, owner):
         return self.released.pop(owner, [])
+
+    def op_register_slabs(self, conn, table):
+        self.slab_tables[table["owner"]] = table
+        return True
+
+    def op_list_slabs(self, conn):
+        return list(self.slab_tables.values())
 
     def op_barrier_arrive(self, conn, tag, size):
         """Returns the arrival count this caller must wait for (a tag can be reused run after run)."""

@@ -181,6 +181,14 @@ class QueueHandle:
         """Producer side: leases of ``owner`` that have been released since the last poll."""
         return self._call("poll_released", owner)
 
+    def register_slabs(self, table):
+        """Producer side: publish the slab ring's handle table once (transport.SlabRing.table())."""
+        return self._call("register_slabs", table)
+
+    def list_slabs(self):
+        """Consumer side: every registered producer's slab table."""
+        return self._call("list_slabs")
+
     def barrier(self, tag, size, timeout=600.0, poll=0.01):
         """Host-side rendezvous standing in for MPI.COMM_WORLD.Barrier() (ref: producer.py:53,120)."""
         target = self._call("barrier_arrive", tag, int(size))

@@ -10,6 +10,13 @@ frames in place -- over NVLink/NVSwitch if it sits on another GPU of the box.
 Slab lifetime: every queued batch carries a lease ``(owner, slab, generation)``; the consumer
 releases it when it moves on (or the queue server does when the consumer's connection drops) and
 the producer reuses a slab only after its lease came back.
+
+Publishing is asynchronous: every slab has an inter-process CUDA event.  The producer queues the
+copies and kernels of a batch, records the slab's event behind them and puts the descriptor at once
+(the reference's put returns only after the data exists, ref: producer.py:99-103); the consumer makes
+its stream wait on that event before it touches the slab, so the queue round trip overlaps the GPU
+work and the next batch's H2D copy.  A producer registers its slab table (memory and event handles)
+with the queue once; consumers map all of it when they connect, not inside the stream.
 """
 from __future__ import annotations
 
@@ -30,6 +37,7 @@ class GpuBatchRef:
     device: int                # producer's CUDA device index
     pid: int = field(default_factory=os.getpid)
     dtype: str = "float32"
+    event: bytes | None = None # cudaIpcEventHandle_t (64 bytes) of the slab's "batch is final" event; None = already final
 
     @property
     def nbytes(self):
@@ -58,30 +66,73 @@ class _CudaArray:
 
 
 class SlabMapper:
-    """Consumer side: opens each producer slab once and hands out tensor views into it."""
+    """Consumer side: opens each producer slab (and its event) once and hands out tensor views into it."""
 
     def __init__(self, device: int = 0):
         from . import _native as N
         self._N = N
         self._lib = N.load()
         self.device = device
-        self._open = {}            # handle bytes -> base pointer
+        self._open = {}            # memory handle bytes -> base pointer
+        self._events = {}          # event handle bytes -> cudaEvent_t
 
-    def map(self, ref: GpuBatchRef):
-        import torch
-        base = self._open.get(ref.handle)
+    def _open_mem(self, handle):
+        base = self._open.get(handle)
         if base is None:
-            if ref.pid == os.getpid():
-                raise RuntimeError("a CUDA-IPC handle cannot be opened in the process that exported it")
             p = C.c_void_p()
-            hb = (C.c_ubyte * self._N.PSR_IPC_HANDLE_BYTES).from_buffer_copy(ref.handle)
+            hb = (C.c_ubyte * self._N.PSR_IPC_HANDLE_BYTES).from_buffer_copy(handle)
             self._N.check(self._lib.psr_ipc_open_mem(hb, self.device, C.byref(p)))
             base = p.value
-            self._open[ref.handle] = base
+            self._open[handle] = base
+        return base
+
+    def _open_event(self, handle):
+        ev = self._events.get(handle)
+        if ev is None:
+            p = C.c_void_p()
+            hb = (C.c_ubyte * self._N.PSR_IPC_HANDLE_BYTES).from_buffer_copy(handle)
+            self._N.check(self._lib.psr_ipc_event_open(hb, self.device, C.byref(p)))
+            ev = p.value
+            self._events[handle] = ev
+        return ev
+
+    def premap(self, tables):
+        """Open every slab and event of the registered producers now (at connect), so that the first batches of a stream
+        do not pay for cudaIpcOpenMemHandle and peer-access set-up.  Tables of producers that are gone are skipped."""
+        n = 0
+        for t in tables:
+            if t.get("pid") == os.getpid():
+                continue
+            for h, e in zip(t.get("handles", ()), t.get("events", ())):
+                try:
+                    self._open_mem(h)
+                    if e is not None:
+                        self._open_event(e)
+                    n += 1
+                except Exception:
+                    break                      # a dead producer's handles cannot be opened
+        return n
+
+    def map(self, ref: GpuBatchRef, stream=None):
+        """Tensor view of the batch; the current (or given) stream is made to wait for the batch to be final first."""
+        import torch
+        if ref.pid == os.getpid() and ref.handle not in self._open:
+            raise RuntimeError("a CUDA-IPC handle cannot be opened in the process that exported it")
+        base = self._open_mem(ref.handle)
+        if ref.event is not None:
+            ev = self._open_event(ref.event)
+            st = stream if stream is not None else torch.cuda.current_stream(torch.device("cuda", self.device)).cuda_stream
+            self._N.check(self._lib.psr_event_wait(C.c_void_p(ev), C.c_void_p(st)))
         arr = _CudaArray(base + ref.offset, ref.shape, owner=self)
         return torch.as_tensor(arr, device=torch.device("cuda", self.device))
 
     def close(self):
+        for ev in self._events.values():
+            try:
+                self._lib.psr_event_destroy(C.c_void_p(ev))
+            except Exception:
+                pass
+        self._events.clear()
         for base in self._open.values():
             try:
                 self._lib.psr_ipc_close_mem(C.c_void_p(base), self.device)
@@ -104,7 +155,7 @@ class SlabRing:
         # plain cudaMalloc blocks (not torch's caching allocator): an IPC handle names a whole allocation,
         # so each slab is its own allocation and a batch sits at offset 0 of it
         nbytes = int(np.prod(self.batch_shape)) * 4
-        self._ptrs, self.slabs, self.handles, self.offsets = [], [], [], []
+        self._ptrs, self.slabs, self.handles, self.offsets, self.events, self.event_handles = [], [], [], [], [], []
         for _ in range(nslabs):
             p = C.c_void_p()
             N.check(self._lib.psr_device_alloc(C.byref(p), nbytes, device))
@@ -115,12 +166,27 @@ class SlabRing:
             N.check(self._lib.psr_ipc_export_mem(p, hb))
             self.handles.append(bytes(hb))
             self.offsets.append(0)
+            ev, eh = C.c_void_p(), (C.c_ubyte * N.PSR_IPC_HANDLE_BYTES)()
+            N.check(self._lib.psr_ipc_event_create(C.byref(ev), eh, device))   # "the batch in this slab is final"
+            self.events.append(ev.value)
+            self.event_handles.append(bytes(eh))
         self.generation = [0] * nslabs
         self.free = list(range(nslabs))
         self.out = {}              # lease -> slab index
 
+    def table(self):
+        """What a consumer needs to map this ring ahead of time (registered with the queue once)."""
+        return {"owner": self.owner, "pid": os.getpid(), "device": self.device, "handles": list(self.handles),
+                "events": list(self.event_handles), "batch_shape": self.batch_shape}
+
     def close(self):
         self.slabs = []
+        for e in self.events:
+            try:
+                self._lib.psr_event_destroy(C.c_void_p(e))
+            except Exception:
+                pass
+        self.events = []
         for p in self._ptrs:
             try:
                 self._lib.psr_device_free(C.c_void_p(p), self.device)
@@ -150,6 +216,6 @@ class SlabRing:
         if i is not None:
             self.free.insert(0, i)
 
-    def ref(self, i, count):
+    def ref(self, i, count, with_event=True):
         shape = (count,) + self.batch_shape[1:]
-        return GpuBatchRef(self.handles[i], self.offsets[i], shape, self.device)
+        return GpuBatchRef(self.handles[i], self.offsets[i], shape, self.device, event=self.event_handles[i] if with_event else None)
