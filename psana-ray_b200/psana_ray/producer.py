@@ -200,6 +200,10 @@ class GpuBatchPipeline:
         self._h_raw_np = self.h_raw.numpy().view(np.uint16)
         self.ring = SlabRing(nslabs, (self.batch_size,) + self.event_shape, device)
         self._registered = False
+        # publishing is asynchronous, but the rank stays at most this many batches ahead of its GPU: without a bound it
+        # would fill the queue in microseconds and spend its time in the reference's put back-off (0.1-2 s per refusal)
+        self.max_in_flight = int(os.environ.get("PSANA_RAY_IN_FLIGHT", "2"))
+        self._in_flight = []
 
     def stage(self, k, raw_frame):
         self._h_raw_np[k] = raw_frame
@@ -213,6 +217,13 @@ class GpuBatchPipeline:
             self._registered = True
         self.ring.reclaim(queue.poll_released(self.ring.owner))
 
+    def _throttle(self, i):
+        from . import _native as N
+        import ctypes as C
+        while len(self._in_flight) >= self.max_in_flight:
+            N.check(self.cal._lib.psr_event_synchronize(C.c_void_p(self.ring.events[self._in_flight.pop(0)])))
+        self._in_flight.append(i)
+
     def process(self, n, queue):
         """Calibrate the n staged frames into a free slab.  Returns (payload, lease) or None if no slab is free."""
         self.poll(queue)
@@ -220,6 +231,7 @@ class GpuBatchPipeline:
         if got is None:
             return None
         i, slab, lease = got
+        self._throttle(i)
         d_out = slab[:n].view((n,) + (self.cal.image_shape if self.image else self.spec.shape))
         # queued, not waited for: the slab's inter-process event is recorded behind the kernels and the descriptor is
         # published at once; only the staging buffer is waited for, because the next events are staged into it
@@ -235,6 +247,7 @@ class GpuBatchPipeline:
         if got is None:
             return None
         i, slab, lease = got
+        self._throttle(i)
         d_out = slab[:n].view((n,) + (self.cal.image_shape if self.image else self.spec.shape))
         # the pool the view comes from is read-only, so nothing is waited for here: the next batch's copies queue up
         # right behind this one's
@@ -253,8 +266,27 @@ class GpuBatchPipeline:
         self.ring.close()
 
 
-def _backoff_put(queue, item, weight, lease, rank, what):
+def _wait_for_room(queue, weight, maxsize, poll=0.0005, limit=5.0):
+    """Additive: look before putting.  A refused put costs the reference's back-off below -- at least 0.1 s, thousands of
+    events at GPU rates -- so a producer that knows the queue's size waits in half-millisecond steps until its batch
+    fits (an empty queue always takes one item).  The put itself and its back-off are unchanged; with several producers
+    a put can still be refused and then backs off exactly as the reference does."""
+    if not maxsize:
+        return
+    t0 = time.time()
+    try:
+        while time.time() - t0 < limit:
+            sz = queue.size()
+            if sz == 0 or sz + weight <= maxsize:
+                return
+            time.sleep(poll)
+    except Exception:
+        return
+
+
+def _backoff_put(queue, item, weight, lease, rank, what, maxsize=None):
     """The reference's blocking put (ref: producer.py:99-117).  Returns False if the queue is dead."""
+    _wait_for_room(queue, weight, maxsize)
     base_delay_in_sec = 0.1
     max_delay_in_sec = 2.0
     retries = 0
@@ -278,7 +310,7 @@ def _backoff_put(queue, item, weight, lease, rank, what):
             time.sleep(1)
 
 
-def produce_batches(source, pipeline, queue, world, max_steps=None, sleep=time.sleep):
+def produce_batches(source, pipeline, queue, world, max_steps=None, sleep=time.sleep, queue_size=None):
     """Batch fast path of the event loop: the source hands out whole batches in pinned memory.  Same items,
     same per-rank index, same back-off as produce_data; returns False if the queue died."""
     rank = world.rank
@@ -299,14 +331,14 @@ def produce_batches(source, pipeline, queue, world, max_steps=None, sleep=time.s
             waits = min(waits + 1, 8)
         payload, lease = res
         item = EventBatch(rank=rank, idx0=idx0, count=n, data=payload, photon_energy=list(energies), lease=lease)
-        if not _backoff_put(queue, item, n, lease, rank, f"idx={idx0}..{idx0 + n - 1}"):
+        if not _backoff_put(queue, item, n, lease, rank, f"idx={idx0}..{idx0 + n - 1}", queue_size):
             return False
         logging.debug(f"Rank {rank} produced: idx={idx0}..{idx0 + n - 1}")
     return True
 
 
 def produce_data(source, pipeline, queue, world, num_consumers=1, max_steps=None, sleep=time.sleep, reliable_sentinels=False,
-                 batch_source=False):
+                 batch_source=False, queue_size=None):
     """The reference's ``produce_data`` (ref: producer.py:78-130) with events grouped into batches.
 
     ``pipeline`` needs ``batch_size``, ``stage(k, raw)``, ``process(n, queue) -> (payload, lease) | None``."""
@@ -328,7 +360,7 @@ def produce_data(source, pipeline, queue, world, num_consumers=1, max_steps=None
             waits = min(waits + 1, 8)
         payload, lease = res
         item = EventBatch(rank=rank, idx0=idx0, count=staged, data=payload, photon_energy=list(energies), lease=lease)
-        ok = _backoff_put(queue, item, staged, lease, rank, f"idx={idx0}..{idx0 + staged - 1} | shape={getattr(payload, 'shape', None)}")
+        ok = _backoff_put(queue, item, staged, lease, rank, f"idx={idx0}..{idx0 + staged - 1} | shape={getattr(payload, 'shape', None)}", queue_size)
         logging.info(f"Rank {rank} produced: idx={idx0}..{idx0 + staged - 1} | shape={tuple(getattr(payload, 'shape', ()))}")
         idx0 += staged
         staged, energies = 0, []
@@ -336,7 +368,7 @@ def produce_data(source, pipeline, queue, world, num_consumers=1, max_steps=None
 
     alive = True
     if batch_source:
-        if not produce_batches(source, pipeline, queue, world, max_steps, sleep):
+        if not produce_batches(source, pipeline, queue, world, max_steps, sleep, queue_size):
             return
     for idx, (raw, photon_energy) in enumerate(source.iter_raw_events() if not batch_source else ()):
         if max_steps is not None and idx >= max_steps:
@@ -423,7 +455,7 @@ def main(argv=None):
         nslabs = max(2, -(-args.queue_size // args.batch_size)) + 2
         pipeline = GpuBatchPipeline(source, psana_mode, device, args.batch_size, nslabs, bad, manual)
         produce_data(source, pipeline, queue, world, args.num_consumers, args.max_steps,
-                     reliable_sentinels=args.reliable_sentinels, batch_source=args.batch_source)
+                     reliable_sentinels=args.reliable_sentinels, batch_source=args.batch_source, queue_size=args.queue_size)
     except Exception as e:
         logging.error(f"Rank {rank}: Unhandled exception in main: {e}")
         logging.error("Traceback:")
