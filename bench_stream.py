@@ -25,7 +25,7 @@ dev = int(sys.argv[1]); torch.cuda.set_device(dev)
 t_deadline = time.time() + 120
 while True:
     try:
-        rd = DataReader(queue_name="stream", ray_namespace="bench", device=dev, zero_copy=True); rd.connect(); break
+        rd = DataReader(queue_name="stream", ray_namespace="bench", device=dev, zero_copy=True, expected_producers=int(sys.argv[2]) if len(sys.argv) > 2 else 0); rd.connect(); break
     except ValueError:
         if time.time() > t_deadline: raise
         time.sleep(0.05)
@@ -220,7 +220,7 @@ def main():
         pargs += ["--common_mode", a.common_mode]
     prods = [subprocess.Popen([sys.executable, "-m", "psana_ray.producer"] + pargs,
                               env=dict(env, RANK=str(r), WORLD_SIZE=str(a.gpus), LOCAL_RANK=str(r))) for r in range(a.gpus)]
-    cons = [subprocess.Popen([sys.executable, cons_src, str(c % a.gpus)], env=env, stdout=subprocess.PIPE, text=True) for c in range(ncons)]
+    cons = [subprocess.Popen([sys.executable, cons_src, str(c % a.gpus), str(a.gpus)], env=env, stdout=subprocess.PIPE, text=True) for c in range(ncons)]
     outs = [json.loads(c.communicate(timeout=240)[0].strip().splitlines()[-1]) for c in cons]
     rcs = [p.wait(timeout=300) for p in prods]
     try:

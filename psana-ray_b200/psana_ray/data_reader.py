@@ -28,13 +28,16 @@ from .transport import EventBatch, GpuBatchRef
 
 
 class DataReader:
-    def __init__(self, address='auto', queue_name="shared_queue", ray_namespace='my', device=None, zero_copy=False, premap=True):
+    def __init__(self, address='auto', queue_name="shared_queue", ray_namespace='my', device=None, zero_copy=False, premap=True,
+                 expected_producers=0, premap_timeout_s=30.0):
         self.address = address
         self.queue_name = queue_name
         self.ray_namespace = ray_namespace
         self.device = device          # CUDA device GPU batches are mapped on; None = current device at first use
         self.zero_copy = zero_copy    # True: hand out views into the producer's slab (see LIFETIME above)
         self.premap = premap          # map every registered producer slab at connect(), not on first touch
+        self.expected_producers = int(expected_producers)   # connect() waits (up to premap_timeout_s) until this many producers
+        self.premap_timeout_s = premap_timeout_s            # have registered their slabs, so all mapping happens before the stream
         self._queue = None
         self._mapper = None
         self._batch = None            # EventBatch being handed out
@@ -52,7 +55,11 @@ class DataReader:
             raise
         if self.premap:
             try:
+                t0 = time.time()
                 tables = self._queue.list_slabs()
+                while len(tables) < self.expected_producers and time.time() - t0 < self.premap_timeout_s:
+                    time.sleep(0.02)
+                    tables = self._queue.list_slabs()
                 if tables:
                     self._ensure_mapper().premap(tables)
             except Exception:

@@ -208,13 +208,18 @@ class GpuBatchPipeline:
     def stage(self, k, raw_frame):
         self._h_raw_np[k] = raw_frame
 
-    def poll(self, queue):
-        if not self._registered:                      # once: consumers map every slab and event when they connect
+    def register(self, queue):
+        """Once, before the first batch: publish the ring's handle table, so that consumers map every slab and event when
+        they connect instead of inside the stream."""
+        if not self._registered:
             try:
                 queue.register_slabs(self.ring.table())
             except Exception:
                 pass
             self._registered = True
+
+    def poll(self, queue):
+        self.register(queue)
         self.ring.reclaim(queue.poll_released(self.ring.owner))
 
     def _throttle(self, i):
@@ -266,7 +271,7 @@ class GpuBatchPipeline:
         self.ring.close()
 
 
-def _wait_for_room(queue, weight, maxsize, poll=0.0005, limit=5.0):
+def _wait_for_room(queue, weight, maxsize, poll=0.0005, limit=5.0, poll_max=0.008):
     """Additive: look before putting.  A refused put costs the reference's back-off below -- at least 0.1 s, thousands of
     events at GPU rates -- so a producer that knows the queue's size waits in half-millisecond steps until its batch
     fits (an empty queue always takes one item).  The put itself and its back-off are unchanged; with several producers
@@ -280,6 +285,7 @@ def _wait_for_room(queue, weight, maxsize, poll=0.0005, limit=5.0):
             if sz == 0 or sz + weight <= maxsize:
                 return
             time.sleep(poll)
+            poll = min(poll * 2, poll_max)        # several waiting producers must not keep the single-threaded queue busy
     except Exception:
         return
 
@@ -454,6 +460,7 @@ def main(argv=None):
         manual = np.load(args.manual_mask_path) if args.manual_mask_path is not None else None
         nslabs = max(2, -(-args.queue_size // args.batch_size)) + 2
         pipeline = GpuBatchPipeline(source, psana_mode, device, args.batch_size, nslabs, bad, manual)
+        pipeline.register(queue)
         produce_data(source, pipeline, queue, world, args.num_consumers, args.max_steps,
                      reliable_sentinels=args.reliable_sentinels, batch_source=args.batch_source, queue_size=args.queue_size)
     except Exception as e:
