@@ -1100,7 +1100,7 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
 // the groups drift apart and fill each other's barrier and latency gaps, like two CTAs that share their
 // 135 KB of constants.  A thread holds 24 pixels (six 4-pixel chunks) of its group's frame.
 // =================================================================================================
-template <bool IMG>
+template <bool IMG, bool KEEP>
 __global__ void __launch_bounds__(704, 1)
 cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c, int nframes, int fpc)
 {
@@ -1148,7 +1148,7 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
         for (int i = 0; i < 4; ++i) {
             const uint32_t fb = (f >> (8 * i)) & 0xFFu;
             const int q = BP::pos(j * 4 + i);
-            kbits |= ((fb & PSR_FL_KEEP) ? 1u : 0u) << q;
+            if (KEEP) kbits |= ((fb & PSR_FL_KEEP) ? 1u : 0u) << q;
             e0bits |= ((fb & PSR_FL_ELIG0) ? 1u : 0u) << q;
             e1bits |= ((fb & PSR_FL_ELIG1) ? 1u : 0u) << q;
         }
@@ -1157,7 +1157,6 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
             if (grp == 0) sgp[(CPT + j) * GT + t] = t0;
         }
     }
-    const bool use_keep = c.has_keep && !c.ignore_keep;           // uniform: np.where(keep, v, 0) only when a keep mask is installed
     const size_t fout = IMG ? (size_t)c.H * c.W : (size_t)c.npix;
     // always 0 (this kernel is epix10ka's), but not to the compiler: lets a value be made to depend on another, which
     // keeps ptxas from hoisting every chunk's loads to the top and spilling the values it has already computed
@@ -1171,7 +1170,7 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
         float* outf = out + (size_t)frame * fout;
         float x[NK];
         uint32_t sbits = 0;                                       // bit BP::pos(i) = data bit 14 of value i
-        asm volatile("" : "+r"(kbits));                           // not loop-invariant to the compiler: it would hoist (and spill) the single-bit tests
+        if (KEEP) asm volatile("" : "+r"(kbits));                 // not loop-invariant to the compiler: it would hoist (and spill) the single-bit tests
         uint2 rv[CPT];
 #pragma unroll
         for (int j = 0; j < CPT; ++j) rv[j] = __ldcs(reinterpret_cast<const uint2*>(rawf + sgp[j * GT + t]));
@@ -1231,7 +1230,7 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
                 const float xv = psr_sub_if(x[j * 4 + i], cm, eligq & (1u << q));
                 o[i] = psr_mul_sel(xv, g0[i], g1[i], sbitsq & (1u << q));
             }
-            if (use_keep) {
+            if (KEEP) {                                               // np.where(keep, v, 0): only the variant launched when a keep mask is installed
 #pragma unroll
                 for (int i = 0; i < 4; ++i) if (!(kbits & (1u << BP::pos(j * 4 + i)))) o[i] = 0.0f;
             }
@@ -1278,9 +1277,11 @@ cudaError_t psr_common_mode_setup(void)
         e = cudaFuncSetAttribute(cm_banks_kernel<1, 512, 1024, 16, PSR_CMB_JF_NT, PSR_CMB_JF_MINB, PSR_CMB_JF_CW, PSR_CMB_JF_KS != 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * 64 * 4);
         if (e != cudaSuccess) return e;
     }
-    e = cudaFuncSetAttribute(cm_banks_epix_groups_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_GROUPS_SMEM);
+    e = cudaFuncSetAttribute(cm_banks_epix_groups_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_GROUPS_SMEM);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(cm_banks_epix_groups_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_GROUPS_SMEM);
+    e = cudaFuncSetAttribute(cm_banks_epix_groups_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_GROUPS_SMEM);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(cm_banks_epix_groups_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_GROUPS_SMEM);
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(cm_calib_kernel<1, 512, 1024, 16, JF_NT>,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JF_SMEM);
@@ -1294,7 +1295,10 @@ cudaError_t launch_banks(const PsrDev& c, const uint16_t* d_raw, int nframes, fl
         if (nframes > 1) {
             const int fpc = PSR_CM_GROUPS_FPC;
             dim3 g2((unsigned)c.nseg * 2 * 8, (unsigned)((nframes + fpc - 1) / fpc));
-            cm_banks_epix_groups_kernel<IMG><<<g2, 704, EPIX_GROUPS_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
+            // the calib-layout keep mask never applies to images (ref: producer.py:92-97 masks the 2-D image), and without an
+            // installed mask every keep bit is set: only calib output with a mask runs the variant that tests them
+            if (!IMG && c.has_keep && !c.ignore_keep) cm_banks_epix_groups_kernel<false, true><<<g2, 704, EPIX_GROUPS_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
+            else cm_banks_epix_groups_kernel<IMG, false><<<g2, 704, EPIX_GROUPS_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
         } else {
             const unsigned grid = (unsigned)nframes * c.nseg * 2 * 8;
             cm_banks_kernel<0, 352, 384, 8, PSR_CMB_EPIX_NT, PSR_CMB_EPIX_MINB, PSR_CMB_EPIX_CW, PSR_CMB_EPIX_KS != 0, IMG>

@@ -15,7 +15,7 @@ import torch
 from psana_ray import _native as N, synthetic as syn
 
 ap = argparse.ArgumentParser()
-ap.add_argument("--workload", default="calib", choices=["calib", "cm", "jungfrau", "image_nocm"])
+ap.add_argument("--workload", default="calib", choices=["calib", "cm", "jungfrau", "image_nocm", "image"])
 ap.add_argument("--libs", nargs="+", default=[N.LIB_PATH])
 ap.add_argument("--fpb", default="0")
 ap.add_argument("--iters", type=int, default=50)
@@ -35,7 +35,7 @@ consts = syn.make_constants(spec, seed=0)
 raw = syn.make_raw_frames(spec, consts, 8, seed=1)
 raw = np.concatenate([raw] * max(1, a.batch // 8))[:a.batch]
 d_raw = torch.from_numpy(raw.view(np.int16)).cuda()
-geo = syn.make_pixel_index_arrays(spec, gap=a.gap) if a.workload == "image_nocm" else None
+geo = syn.make_pixel_index_arrays(spec, gap=a.gap) if a.workload in ("image_nocm", "image") else None
 if geo is not None and a.geo != "default":
     R, Cc = spec.rows, spec.cols
     r, c = np.meshgrid(np.arange(R), np.arange(Cc), indexing="ij")
@@ -63,7 +63,7 @@ for path in libs:
     assert lib.psr_set_constants(ctx, p(consts["peds"]), p(consts.get("gain")), p(consts.get("offs")), p(consts.get("cfg")), p(consts.get("mask")), spec.nmodes) == 0, lib.psr_last_error()
     out_kind = 0
     nout = spec.npix
-    if a.workload == "cm":
+    if a.workload in ("cm", "image"):
         lib.psr_set_common_mode(ctx, a.cm_mode, C.c_float(100.0), a.npix_min, 0)
     if geo is not None:
         assert lib.psr_set_geometry(ctx, p(geo[0]), p(geo[1])) == 0
