@@ -50,6 +50,12 @@
 #ifndef PSR_CMF_OPAQUE
 #define PSR_CMF_OPAQUE 1
 #endif
+#ifndef PSR_LQ_NARROW_M          /* linear median: halve the window when the median's bin holds more values than this (and the tails are empty) */
+#define PSR_LQ_NARROW_M 24
+#endif
+#ifndef PSR_LQ_MIN_WINDOW        /* linear median: narrowest window, ADU */
+#define PSR_LQ_MIN_WINDOW 16.0f
+#endif
 #ifndef PSR_CM_MATCH
 #define PSR_CM_MATCH 0
 #endif
@@ -621,7 +627,7 @@ __device__ __noinline__ void lq_median_slow(const float* xs, uint32_t elig, int 
 // half as wide when the median's bin was crowded and the tails are empty.  Returns false (uniformly) when fewer than
 // max(npix_min, 1) values are eligible; else lo/hi = the two middle order statistics.  Every thread of the group must call it.
 struct LqWindow { float a, b; };
-constexpr float LQ_A_MIN = LQ_A_COARSE * 2.0f;
+constexpr float LQ_A_MIN = LQ_A_COARSE * 2.0f, LQ_A_MAX = 1.0f / PSR_LQ_MIN_WINDOW;
 
 template <int NT, int NK, int CAP, typename BP, typename X, typename G>
 __device__ __forceinline__ bool block_median_linear(const X& x, uint32_t elig, int npix_min, LqWindow& win,
@@ -651,8 +657,8 @@ __device__ __forceinline__ bool block_median_linear(const X& x, uint32_t elig, i
     float na = a;
     if (tails * 2 > n) na = a * 0.25f;
     else if (tails * 8 > n) na = a * 0.5f;
-    else if (M > 96 && tails * 32 < n) na = a * 2.0f;
-    na = fminf(fmaxf(na, LQ_A_MIN), LQ_A);
+    else if (M > PSR_LQ_NARROW_M && tails * 32 < n) na = a * 2.0f;
+    na = fminf(fmaxf(na, LQ_A_MIN), LQ_A_MAX);
     const float nb = __fsub_rn(0.5f, __fmul_rn(psr_mid(lo, hi), na));                     // a wild value just costs that frame a relocation
     win.a = na; win.b = fabsf(nb) < 1.0e6f ? nb : 0.5f;
     return true;
