@@ -56,6 +56,12 @@
 #ifndef PSR_LQ_MIN_WINDOW        /* linear median: narrowest window, ADU */
 #define PSR_LQ_MIN_WINDOW 16.0f
 #endif
+#ifndef PSR_CM_WORDS_GROUPS       /* epix10ka batches, words with row / column medians: 1 = the two-frame-group kernel, 0 = cm_calib_kernel */
+#define PSR_CM_WORDS_GROUPS 1
+#endif
+#ifndef PSR_CM_WORDS_NG           /* that kernel's frame groups per CTA: 1 = all 704 threads on one frame (12 values per thread), 2 = two groups of 352 */
+#define PSR_CM_WORDS_NG 1
+#endif
 #ifndef PSR_CM_MATCH
 #define PSR_CM_MATCH 0
 #endif
@@ -1099,6 +1105,233 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
 }
 
 // =================================================================================================
+// Many small medians at once (the row and column sub-modes): one linear histogram PER SEGMENT -- a row of a bank
+// (48 values) or a column of a half (176 values) -- with byte counters (a segment holds at most 176 values), all
+// segments of the tile filled in one pass over the values the threads hold in registers.  As for the bank median
+// the bin function is monotone, so the bin where a segment's cumulative count crosses rank (n - 1) / 2 holds that
+// order statistic; its members -- and those of the next occupied bin when the upper middle value lies there -- are
+// collected per segment and ranked.  A segment whose rank falls into an end bin, or whose bins hold more than CAP
+// values, is redone exactly, one at a time, from a list of all its values (seg_slow).
+//
+// Shared memory per group (SegBuf): `buf` holds the histograms (NSEG x NB bytes) and, once they are scanned, the
+// candidate lists (NSEG x CAP floats) in the same place.
+// =================================================================================================
+constexpr int SEG_MAX = 176;                       // most segments of one phase (rows of a bank tile)
+constexpr int SEG_BUF_BYTES = 12288;               // rows: 176 x 64 bins / 176 x 16 floats; columns: 48 x 256 bins / 48 x 64 floats
+constexpr int SEG_SMEM_BYTES = SEG_BUF_BYTES + 4 * (3 * SEG_MAX + 8 + SEG_MAX);
+
+struct SegBuf {
+    uint32_t* buf;       // histograms, then candidate lists
+    uint32_t* info;      // per segment: B | B2 << 8 | r << 16 | n << 24 (n = 0: nothing to collect)
+    int* cnt;            // per segment: candidates collected
+    float* cmv;          // per segment: the correction its eligible pixels subtract (0 = none)
+    int* misc;           // 0: failed segments, 1: values in end bins, 2: values in all, 3: slow-path counter, 4: sum of medians (float bits)
+    int* fails;          // ids of the failed segments
+    __device__ __forceinline__ explicit SegBuf(uint8_t* base) {
+        buf = reinterpret_cast<uint32_t*>(base);
+        info = buf + SEG_BUF_BYTES / 4; cnt = reinterpret_cast<int*>(info + SEG_MAX);
+        cmv = reinterpret_cast<float*>(cnt + SEG_MAX); misc = reinterpret_cast<int*>(cmv + SEG_MAX); fails = misc + 8;
+    }
+};
+
+template <int NB>
+__device__ __forceinline__ uint32_t lq_bin8(float x, float a, float b) {            // bin of x in an NB-bin window (NB <= 256)
+    return __float_as_uint(__fmaf_rd(__saturatef(__fmaf_rn(x, a, b)), (float)(NB - 1), 8388608.0f)) & 0xFFu;
+}
+
+// psana's guards for the row / column corrections: apply only where n > npix_min and |cm| < cormax (both strict)
+__device__ __forceinline__ float seg_guard(float lo, float hi, int n, int npix_min, float cormax) {
+    const float cm = psr_mid(lo, (n & 1) ? lo : hi);
+    return (n > npix_min && fabsf(cm) < cormax) ? cm : 0.0f;
+}
+
+// Exact redo of one segment from the list of ALL its eligible values (in sb.buf, n of them): warp 0 ranks them by counting.
+template <typename G>
+__device__ __noinline__ void seg_slow_rank(const SegBuf sb, int seg, int npix_min, float cormax, G g)
+{
+    const int tid = g.tid(), lane = tid & 31;
+    const int n = sb.misc[3];
+    if (tid < 32) {
+        const float* v = reinterpret_cast<const float*>(sb.buf);
+        const int k1 = (n - 1) >> 1, k2 = n >> 1;
+        float lo = 0.f, hi = 0.f; bool flo = false, fhi = false;
+        for (int i = lane; i < n; i += 32) {
+            const float vi = v[i];
+            int lt = 0, le = 0;
+            for (int j = 0; j < n; ++j) { const float u = v[j]; lt += (u < vi); le += (u <= vi); }
+            if (lt <= k1 && k1 < le) { lo = vi; flo = true; }
+            if (lt <= k2 && k2 < le) { hi = vi; fhi = true; }
+        }
+        const uint32_t mlo = __ballot_sync(0xFFFFFFFFu, flo), mhi = __ballot_sync(0xFFFFFFFFu, fhi);
+        if (n > 0) {
+            lo = __shfl_sync(0xFFFFFFFFu, lo, __ffs(mlo) - 1);
+            hi = __shfl_sync(0xFFFFFFFFu, hi, __ffs(mhi) - 1);
+            if (lane == 0) sb.cmv[seg] = seg_guard(lo, hi, n, npix_min, cormax);
+        } else if (lane == 0) sb.cmv[seg] = 0.0f;
+    }
+    g.sync();
+}
+
+// x: the thread's NK values; elig: bit BP::pos(i) = value i takes part; SEG::of(i) = the segment of value i (SEG::base(j) may
+// hoist per-chunk work).  On return sb.cmv[seg] holds every segment's correction (guards applied); win is updated.
+// Every thread of the group must call it.
+template <int GT, int NK, int NSEG, int NB, int TPS, int CAP, typename BP, typename SEG, typename G>
+__device__ __forceinline__ void seg_medians(const float (&x)[NK], uint32_t elig, const SEG& sg, int npix_min, float cormax, LqWindow& win,
+                                            const SegBuf sb, const G& g)
+{
+    static_assert(NSEG * NB <= SEG_BUF_BYTES && NSEG * CAP * 4 <= SEG_BUF_BYTES && NSEG <= SEG_MAX && NSEG * TPS <= GT, "segment layout");
+    static_assert((NB / 4) % TPS == 0 && (NB / 4 / TPS) % 4 == 0 && (TPS & (TPS - 1)) == 0 && NB <= 256 && CAP % 4 == 0, "scan layout");
+    constexpr int W = NB / 4 / TPS;                  // histogram words one scanning thread owns
+    const int tid = g.tid(), lane = tid & 31;
+    const float a = win.a, b = win.b;
+    const uint32_t baddr = (uint32_t)__cvta_generic_to_shared(sb.buf);
+
+    // ---- clear ---------------------------------------------------------------------------------------------------
+    for (int i = tid; i < NSEG * NB / 16; i += GT) reinterpret_cast<uint4*>(sb.buf)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < NSEG; i += GT) sb.cnt[i] = 0;
+    if (tid < 8) sb.misc[tid] = 0;
+    g.sync();
+    // ---- histograms: byte counters, one 32-bit add per value (ineligible: add 0) -----------------------------------
+#pragma unroll
+    for (int i = 0; i < NK; ++i) {
+        const uint32_t bin = lq_bin8<NB>(x[i], a, b);
+        const uint32_t m = (elig << (31 - BP::pos(i))) >> 31;
+        asm volatile("red.shared.add.u32 [%0], %1;" :: "r"(baddr + (uint32_t)sg.of(i) * NB + (bin & ~3u)), "r"(m << ((bin & 3u) * 8u)) : "memory");
+    }
+    g.sync();
+    // ---- scan: TPS threads per segment ------------------------------------------------------------------------------
+    const int seg = tid / TPS, part = tid % TPS;
+    uint32_t myinfo = 0; bool writer = false, failed = false;
+    if (tid < NSEG * TPS) {
+        uint32_t w[W];
+        const uint4* h4 = reinterpret_cast<const uint4*>(sb.buf + seg * (NB / 4) + part * W);
+#pragma unroll
+        for (int i = 0; i < W / 4; ++i) { const uint4 u = h4[i]; w[4 * i] = u.x; w[4 * i + 1] = u.y; w[4 * i + 2] = u.z; w[4 * i + 3] = u.w; }
+        uint32_t ps = 0; int fne = 255;              // bytewise sums (no byte exceeds the segment's size < 256); first occupied bin of this part
+#pragma unroll
+        for (int i = W - 1; i >= 0; --i) { ps += w[i]; if (w[i]) fne = 4 * (part * W + i) + ((__ffs(w[i]) - 1) >> 3); }
+        const uint32_t ptot = (ps * 0x01010101u) >> 24;
+        uint32_t n = 0, carry = 0; int fnext = 255;
+#pragma unroll
+        for (int p = TPS - 1; p >= 0; --p) {
+            const uint32_t tp = __shfl_sync(0xFFFFFFFFu, ptot, (lane & ~(TPS - 1)) + p);
+            const int fp = __shfl_sync(0xFFFFFFFFu, fne, (lane & ~(TPS - 1)) + p);
+            n += tp; if (p < part) carry += tp; if (p > part && fp != 255) fnext = fp;          // descending p: ends at the nearest higher part
+        }
+        if (part == 0) {                              // window statistics: what fell into the two end bins
+            int tails = (int)(w[0] & 0xFFu);
+            if (TPS == 1) tails += (int)(w[W - 1] >> 24);
+            if (tails) atomicAdd(&sb.misc[1], tails);
+            if (n) atomicAdd(&sb.misc[2], (int)n);
+        } else if (part == TPS - 1) { const int tails = (int)(w[W - 1] >> 24); if (tails) atomicAdd(&sb.misc[1], tails); }
+        const uint32_t k1 = n ? (n - 1) >> 1 : 0;
+        if (n == 0) { writer = part == 0; myinfo = 0; }
+        else if (k1 >= carry && k1 < carry + ptot) {
+            writer = true;
+            uint32_t cum = carry; int B = -1, B2 = 255; uint32_t r = 0, M = 0;
+#pragma unroll
+            for (int i = 0; i < W; ++i) {
+                const uint32_t pre = w[i] * 0x01010101u, tw = pre >> 24;          // byte k of pre = w's bytes 0..k summed
+                if (B < 0 && k1 < cum + tw) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint32_t ck = cum + ((pre >> (8 * k)) & 0xFFu), bk = (w[i] >> (8 * k)) & 0xFFu;
+                        if (B < 0 && ck > k1) {
+                            B = 4 * (part * W + i) + k; M = bk; r = k1 - (ck - bk);
+                            const uint32_t rest = k < 3 ? (w[i] >> (8 * (k + 1))) : 0u;
+                            if (rest) B2 = B + 1 + ((__ffs(rest) - 1) >> 3);
+                        }
+                    }
+                } else if (B >= 0 && B2 == 255 && w[i]) B2 = 4 * (part * W + i) + ((__ffs(w[i]) - 1) >> 3);
+                cum += tw;
+            }
+            if (B2 == 255) B2 = fnext;
+            const bool need_hi = (n & 1u) == 0u && r + 1 >= M;                       // the upper middle value lies in the next occupied bin
+            uint32_t M2 = 0;
+            if (need_hi && B2 != 255) M2 = reinterpret_cast<const uint8_t*>(sb.buf)[seg * NB + B2];
+            failed = B <= 0 || B >= NB - 1 || (need_hi && (B2 == 255 || B2 >= NB - 1)) || M + M2 > (uint32_t)CAP;
+            myinfo = failed ? 0u : ((uint32_t)B | ((need_hi ? (uint32_t)B2 : (uint32_t)B) << 8) | (r << 16) | (n << 24));
+        }
+    }
+    g.sync();                                         // every histogram word has been read: buf becomes the candidate lists
+    if (writer) {
+        sb.info[seg] = myinfo;
+        if (failed) sb.fails[atomicAdd(&sb.misc[0], 1)] = seg;
+    }
+    g.sync();
+    // ---- collect the members of each segment's one or two bins ------------------------------------------------------
+    float* lists = reinterpret_cast<float*>(sb.buf);
+#pragma unroll
+    for (int i = 0; i < NK; ++i) {
+        const int s = sg.of(i);
+        const uint32_t inf = sb.info[s], bin = lq_bin8<NB>(x[i], a, b);
+        if ((inf >> 24) != 0u && (elig & (1u << BP::pos(i))) && (bin == (inf & 0xFFu) || bin == ((inf >> 8) & 0xFFu))) {
+            const int slot = atomicAdd(&sb.cnt[s], 1);
+            if (slot < CAP) lists[s * CAP + slot] = x[i];
+        }
+    }
+    g.sync();
+    // ---- rank: the TPS threads of a segment share its candidates ----------------------------------------------------
+    if (tid < NSEG * TPS) {
+        const uint32_t inf = sb.info[seg];
+        const int n = (int)(inf >> 24), r = (int)((inf >> 16) & 0xFFu), M = min(sb.cnt[seg], CAP);
+        const float* L = lists + seg * CAP;
+        uint32_t lo = 0, hi = 0; bool flo = false, fhi = false;
+        if (n > 0) {
+            for (int i = part; i < M; i += TPS) {
+                const float v = L[i];
+                int lt = 0, le = 0;
+                for (int j = 0; j < M; ++j) { const float u = L[j]; lt += (u < v); le += (u <= v); }
+                if (lt <= r && r < le) { lo = __float_as_uint(v); flo = true; }
+                if (lt <= r + 1 && r + 1 < le) { hi = __float_as_uint(v); fhi = true; }
+            }
+        }
+#pragma unroll
+        for (int d = 1; d < TPS; d <<= 1) {           // any finder's value (equal values rank equal)
+            const uint32_t olo = __shfl_xor_sync(0xFFFFFFFFu, lo, d), ohi = __shfl_xor_sync(0xFFFFFFFFu, hi, d);
+            const bool oflo = __shfl_xor_sync(0xFFFFFFFFu, (int)flo, d) != 0, ofhi = __shfl_xor_sync(0xFFFFFFFFu, (int)fhi, d) != 0;
+            if (!flo && oflo) { lo = olo; flo = true; }
+            if (!fhi && ofhi) { hi = ohi; fhi = true; }
+        }
+        if (part == 0) sb.cmv[seg] = n > 0 ? seg_guard(__uint_as_float(lo), __uint_as_float(fhi ? hi : lo), n, npix_min, cormax) : 0.0f;
+    }
+    g.sync();
+    // ---- the segments that did not fit the window, exactly, one at a time (uniform; none on ordinary data) ---------
+    const int nfail = sb.misc[0];
+    for (int f = 0; f < nfail; ++f) {
+        const int fs = sb.fails[f];
+        if (tid == 0) sb.misc[3] = 0;
+        g.sync();
+#pragma unroll
+        for (int i = 0; i < NK; ++i)
+            if (sg.of(i) == fs && (elig & (1u << BP::pos(i)))) lists[atomicAdd(&sb.misc[3], 1)] = x[i];
+        g.sync();
+        seg_slow_rank(sb, fs, npix_min, cormax, g);
+    }
+    // ---- next frame's window: twice as wide when an eighth of the values fell outside, half when nothing did ------
+    const int tails = sb.misc[1], ntot = sb.misc[2];
+    float na = a;
+    if (tails * 2 > ntot) na = a * 0.25f;
+    else if (tails * 8 > ntot || nfail * 16 > NSEG) na = a * 0.5f;
+    else if (tails * 64 < ntot && nfail == 0) na = a * 2.0f;
+    win.a = fminf(fmaxf(na, LQ_A_MIN), 1.0f / 32.0f);
+    win.b = 0.5f;                                     // rows and columns are corrected around the bank level: centred on 0
+    g.sync();                                         // cmv is final and misc may be reused
+}
+
+// the segment of value i of thread t of a group of GT threads (chunk j = i / 4 of the thread is chunk t + GT j of the tile, 12 chunks per row)
+template <int GT>
+struct SegRows {            // segment = row of the tile (48 values)
+    int t;
+    __device__ __forceinline__ int of(int i) const { return (t + GT * (i >> 2)) / 12; }
+};
+template <int GT>
+struct SegCols {            // segment = column of the tile (176 values)
+    int t;
+    __device__ __forceinline__ int of(int i) const { const int ch = t + GT * (i >> 2); return 4 * (ch - 12 * (ch / 12)) + (i & 3); }
+};
+
+// =================================================================================================
 // epix10ka, mode 4, TWO FRAME GROUPS: one 704-thread CTA per SM owns one bank tile and walks `fpc` frames of the
 // batch, with ALL of the tile's constants (both pedestal and both gain-factor entries, 135 KB) staged once in
 // shared memory, so the frame loop's global traffic is raw in and floats out, nothing else.  The CTA is two groups of 352 threads that each take
@@ -1106,17 +1339,18 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
 // the groups drift apart and fill each other's barrier and latency gaps, like two CTAs that share their
 // 135 KB of constants.  A thread holds 24 pixels (six 4-pixel chunks) of its group's frame.
 // =================================================================================================
-template <bool IMG, bool KEEP>
+template <bool IMG, bool KEEP, bool WORDS, int NG>
 __global__ void __launch_bounds__(704, 1)
 cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c, int nframes, int fpc)
 {
-    constexpr int NT = 704, NG = 2, GT = NT / NG, ROWS = 352, COLS = 384, NB = 8, TR = ROWS / 2, TC = COLS / NB, CH = TC / 4, NCH = TR * CH;
-    constexpr int CPT = NCH / GT, NK = CPT * 4, CAP = GT;
+    constexpr int NT = 704, GT = NT / NG, ROWS = 352, COLS = 384, NB = 8, TR = ROWS / 2, TC = COLS / NB, CH = TC / 4, NCH = TR * CH;
+    constexpr int CPT = NCH / GT, NK = CPT * 4, CAP = GT > 512 ? 512 : GT;
     using BP = BitsEpixWords4;
-    static_assert(NCH % NT == 0 && NCH % GT == 0 && CPT == 6, "tile layout");
+    static_assert(NCH % NT == 0 && NCH % GT == 0 && (NG == 1 || NG == 2), "tile layout");
     extern __shared__ float4 sm4[];                               // [4][NCH]: ped0, ped1, gf0, gf1 of the 4 pixels of a chunk
     int* sgp = reinterpret_cast<int*>(sm4 + 4 * NCH);             // [CPT][GT] first pixel of a thread's chunk; IMG: + [CPT][GT] its image index
     __shared__ int redbuf[NG][64];
+    static_assert(!(IMG && WORDS), "row / column words write the calib layout (images go through the scratch + gather)");
     __shared__ __align__(16) uint32_t hist[NG][LQ_NB];
     __shared__ __align__(16) float list[NG][CAP + 4];
     __shared__ __align__(16) int selsh[NG][48];
@@ -1171,6 +1405,8 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
 
     const WarpGroup<GT> g{t, 1 + grp};
     LqWindow win{LQ_A, 0.5f};                                     // 64 ADU centred on 0, then following the group's medians and their spread
+    LqWindow winr{LQ_A, 0.5f}, winc{LQ_A, 0.5f};                  // WORDS: the windows of the row and column histograms
+    const SegBuf sb(reinterpret_cast<uint8_t*>(sgp + 2 * CPT * GT) + (WORDS ? grp * SEG_SMEM_BYTES : 0));
     for (int frame = f_begin + grp; frame < f_end; frame += NG) {
         const uint16_t* rawf = raw + (size_t)frame * c.npix;
         float* outf = out + (size_t)frame * fout;
@@ -1214,9 +1450,33 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
 
         // common_mode_2d: skip if n < npix_min, skip if |cm| > cormax.  An unapplied correction is cm = +0: x - 0 == x for every x.
         float lo, hi, cm = 0.f;
-        if (block_median_linear<GT, NK, CAP, BP>(x, elig, c.npix_min, win, &hist[grp][0], &selsh[grp][0], &list[grp][0], &redbuf[grp][0], lo, hi, g)) {
-            const float med = psr_mid(lo, hi);
-            if (!(fabsf(med) > c.cormax)) cm = med;
+        if (!WORDS || (c.cm_mode & 4)) {
+            if (block_median_linear<GT, NK, CAP, BP>(x, elig, c.npix_min, win, &hist[grp][0], &selsh[grp][0], &list[grp][0], &redbuf[grp][0], lo, hi, g)) {
+                const float med = psr_mid(lo, hi);
+                if (!(fabsf(med) > c.cormax)) cm = med;
+            }
+        }
+        if constexpr (WORDS) {
+            // psana's order: bank medians (4), then row medians (1), then column medians (2), each on what the previous left
+            if (c.cm_mode & 4) {
+#pragma unroll
+                for (int i = 0; i < NK; ++i) x[i] = psr_sub_if(x[i], cm, elig & (1u << BP::pos(i)));
+                cm = 0.f;
+            }
+            if (c.cm_mode & 1) {
+                const SegRows<GT> sr{t};
+                seg_medians<GT, NK, 176, 64, 2 * (2 / NG), 16, BP>(x, elig, sr, c.npix_min, c.cormax, winr, sb, g);
+#pragma unroll
+                for (int i = 0; i < NK; ++i) x[i] = psr_sub_if(x[i], sb.cmv[sr.of(i)], elig & (1u << BP::pos(i)));
+                g.sync();                                             // cmv is read before the column phase rewrites it
+            }
+            if (c.cm_mode & 2) {
+                const SegCols<GT> sc{t};
+                seg_medians<GT, NK, 48, 256, 4 * (2 / NG), 64, BP>(x, elig, sc, c.npix_min, c.cormax, winc, sb, g);
+#pragma unroll
+                for (int i = 0; i < NK; ++i) x[i] = psr_sub_if(x[i], sb.cmv[sc.of(i)], elig & (1u << BP::pos(i)));
+                g.sync();
+            }
         }
 
         chain = 0;
@@ -1268,7 +1528,8 @@ constexpr size_t JF_SMEM = ((size_t)(256 * 65) * 5 + 15) / 16 * 16 + (JF_NT / 32
 #ifndef PSR_CM_GROUPS_FPC
 #define PSR_CM_GROUPS_FPC 16   /* frames per CTA of the two-frame-group kernel (8 per group) */
 #endif
-constexpr size_t EPIX_GROUPS_SMEM = (size_t)2112 * (4 * 16) + (size_t)12 * 352 * 4;   // all four constant tables of one bank tile + per-thread chunk offsets
+constexpr size_t EPIX_GROUPS_SMEM = (size_t)2112 * (4 * 16) + (size_t)12 * 352 * 4;
+constexpr size_t EPIX_WORDS_SMEM = EPIX_GROUPS_SMEM + 2 * (size_t)SEG_SMEM_BYTES;   // + the row / column histograms of the two groups   // all four constant tables of one bank tile + per-thread chunk offsets
 
 }  // namespace
 
@@ -1283,11 +1544,15 @@ cudaError_t psr_common_mode_setup(void)
         e = cudaFuncSetAttribute(cm_banks_kernel<1, 512, 1024, 16, PSR_CMB_JF_NT, PSR_CMB_JF_MINB, PSR_CMB_JF_CW, PSR_CMB_JF_KS != 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * 64 * 4);
         if (e != cudaSuccess) return e;
     }
-    e = cudaFuncSetAttribute(cm_banks_epix_groups_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_GROUPS_SMEM);
+    e = cudaFuncSetAttribute(cm_banks_epix_groups_kernel<false, false, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_GROUPS_SMEM);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(cm_banks_epix_groups_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_GROUPS_SMEM);
+    e = cudaFuncSetAttribute(cm_banks_epix_groups_kernel<false, true, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_GROUPS_SMEM);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(cm_banks_epix_groups_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_GROUPS_SMEM);
+    e = cudaFuncSetAttribute(cm_banks_epix_groups_kernel<true, false, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_GROUPS_SMEM);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(cm_banks_epix_groups_kernel<false, false, true, PSR_CM_WORDS_NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_WORDS_SMEM);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(cm_banks_epix_groups_kernel<false, true, true, PSR_CM_WORDS_NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EPIX_WORDS_SMEM);
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(cm_calib_kernel<1, 512, 1024, 16, JF_NT>,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JF_SMEM);
@@ -1303,8 +1568,8 @@ cudaError_t launch_banks(const PsrDev& c, const uint16_t* d_raw, int nframes, fl
             dim3 g2((unsigned)c.nseg * 2 * 8, (unsigned)((nframes + fpc - 1) / fpc));
             // the calib-layout keep mask never applies to images (ref: producer.py:92-97 masks the 2-D image), and without an
             // installed mask every keep bit is set: only calib output with a mask runs the variant that tests them
-            if (!IMG && c.has_keep && !c.ignore_keep) cm_banks_epix_groups_kernel<false, true><<<g2, 704, EPIX_GROUPS_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
-            else cm_banks_epix_groups_kernel<IMG, false><<<g2, 704, EPIX_GROUPS_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
+            if (!IMG && c.has_keep && !c.ignore_keep) cm_banks_epix_groups_kernel<false, true, false, 2><<<g2, 704, EPIX_GROUPS_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
+            else cm_banks_epix_groups_kernel<IMG, false, false, 2><<<g2, 704, EPIX_GROUPS_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
         } else {
             const unsigned grid = (unsigned)nframes * c.nseg * 2 * 8;
             cm_banks_kernel<0, 352, 384, 8, PSR_CMB_EPIX_NT, PSR_CMB_EPIX_MINB, PSR_CMB_EPIX_CW, PSR_CMB_EPIX_KS != 0, IMG>
@@ -1323,6 +1588,14 @@ cudaError_t psr_launch_common_mode(const PsrDev& c, const uint16_t* d_raw, int n
 {
     if (nframes <= 0) return cudaSuccess;
     if (c.cm_mode == 4) return launch_banks<false>(c, d_raw, nframes, d_out, st);
+    if (c.det_kind == 0 && nframes > 1 && PSR_CM_WORDS_GROUPS) {
+        // any word with row / column medians, epix10ka batches: the two-frame-group kernel with its row and column phases
+        const int fpc = PSR_CM_GROUPS_FPC;
+        dim3 g2((unsigned)c.nseg * 2 * 8, (unsigned)((nframes + fpc - 1) / fpc));
+        if (c.has_keep && !c.ignore_keep) cm_banks_epix_groups_kernel<false, true, true, PSR_CM_WORDS_NG><<<g2, 704, EPIX_WORDS_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
+        else cm_banks_epix_groups_kernel<false, false, true, PSR_CM_WORDS_NG><<<g2, 704, EPIX_WORDS_SMEM, st>>>(d_raw, d_out, c, nframes, fpc);
+        return cudaGetLastError();
+    }
     if (c.det_kind == 0) {
         const unsigned grid = (unsigned)nframes * c.nseg * 2 * 8;
         cm_calib_kernel<0, 352, 384, 8, EPIX_NT><<<grid, EPIX_NT, EPIX_SMEM, st>>>(d_raw, d_out, c);
