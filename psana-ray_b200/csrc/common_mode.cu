@@ -1117,7 +1117,7 @@ cm_banks_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
 // candidate lists (NSEG x CAP floats) in the same place.
 // =================================================================================================
 constexpr int SEG_MAX = 176;                       // most segments of one phase (rows of a bank tile)
-constexpr int SEG_BUF_BYTES = 12288;               // rows: 176 x 64 bins / 176 x 16 floats; columns: 48 x 256 bins / 48 x 64 floats
+constexpr int SEG_BUF_BYTES = 13056;               // rows: 176 x 64 bins / 176 x 16 floats; columns: 48 x (256 bins + 16 bytes of skew) / 48 x 64 floats
 constexpr int SEG_SMEM_BYTES = SEG_BUF_BYTES + 4 * (3 * SEG_MAX + 8 + SEG_MAX);
 
 struct SegBuf {
@@ -1179,7 +1179,10 @@ template <int GT, int NK, int NSEG, int NB, int TPS, int CAP, typename BP, typen
 __device__ __forceinline__ void seg_medians(const float (&x)[NK], uint32_t elig, const SEG& sg, int npix_min, float cormax, LqWindow& win,
                                             const SegBuf sb, const G& g)
 {
-    static_assert(NSEG * NB <= SEG_BUF_BYTES && NSEG * CAP * 4 <= SEG_BUF_BYTES && NSEG <= SEG_MAX && NSEG * TPS <= GT, "segment layout");
+    // a segment's histogram starts STRIDE bytes after its neighbour's: with NB a multiple of 128 the plain layout would put
+    // bin b of EVERY segment into the same bank, and a warp's lanes -- different segments, similar bins -- would collide
+    constexpr int STRIDE = (NB % 128 == 0) ? NB + 16 : NB;
+    static_assert(NSEG * STRIDE <= SEG_BUF_BYTES && NSEG * CAP * 4 <= SEG_BUF_BYTES && NSEG <= SEG_MAX && NSEG * TPS <= GT, "segment layout");
     static_assert((NB / 4) % TPS == 0 && (NB / 4 / TPS) % 4 == 0 && (TPS & (TPS - 1)) == 0 && NB <= 256 && CAP % 4 == 0, "scan layout");
     constexpr int W = NB / 4 / TPS;                  // histogram words one scanning thread owns
     const int tid = g.tid(), lane = tid & 31;
@@ -1187,7 +1190,7 @@ __device__ __forceinline__ void seg_medians(const float (&x)[NK], uint32_t elig,
     const uint32_t baddr = (uint32_t)__cvta_generic_to_shared(sb.buf);
 
     // ---- clear ---------------------------------------------------------------------------------------------------
-    for (int i = tid; i < NSEG * NB / 16; i += GT) reinterpret_cast<uint4*>(sb.buf)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < NSEG * STRIDE / 16; i += GT) reinterpret_cast<uint4*>(sb.buf)[i] = make_uint4(0, 0, 0, 0);
     for (int i = tid; i < NSEG; i += GT) sb.cnt[i] = 0;
     if (tid < 8) sb.misc[tid] = 0;
     g.sync();
@@ -1196,7 +1199,7 @@ __device__ __forceinline__ void seg_medians(const float (&x)[NK], uint32_t elig,
     for (int i = 0; i < NK; ++i) {
         const uint32_t bin = lq_bin8<NB>(x[i], a, b);
         const uint32_t m = (elig << (31 - BP::pos(i))) >> 31;
-        asm volatile("red.shared.add.u32 [%0], %1;" :: "r"(baddr + (uint32_t)sg.of(i) * NB + (bin & ~3u)), "r"(m << ((bin & 3u) * 8u)) : "memory");
+        asm volatile("red.shared.add.u32 [%0], %1;" :: "r"(baddr + (uint32_t)sg.of(i) * STRIDE + (bin & ~3u)), "r"(m << ((bin & 3u) * 8u)) : "memory");
     }
     g.sync();
     // ---- scan: TPS threads per segment ------------------------------------------------------------------------------
@@ -1204,7 +1207,7 @@ __device__ __forceinline__ void seg_medians(const float (&x)[NK], uint32_t elig,
     uint32_t myinfo = 0; bool writer = false, failed = false;
     if (tid < NSEG * TPS) {
         uint32_t w[W];
-        const uint4* h4 = reinterpret_cast<const uint4*>(sb.buf + seg * (NB / 4) + part * W);
+        const uint4* h4 = reinterpret_cast<const uint4*>(sb.buf + seg * (STRIDE / 4) + part * W);
 #pragma unroll
         for (int i = 0; i < W / 4; ++i) { const uint4 u = h4[i]; w[4 * i] = u.x; w[4 * i + 1] = u.y; w[4 * i + 2] = u.z; w[4 * i + 3] = u.w; }
         uint32_t ps = 0; int fne = 255;              // bytewise sums (no byte exceeds the segment's size < 256); first occupied bin of this part
@@ -1251,7 +1254,7 @@ __device__ __forceinline__ void seg_medians(const float (&x)[NK], uint32_t elig,
             if (B2 == 255) B2 = fnext;
             const bool need_hi = (n & 1u) == 0u && r + 1 >= M;                       // the upper middle value lies in the next occupied bin
             uint32_t M2 = 0;
-            if (need_hi && B2 != 255) M2 = reinterpret_cast<const uint8_t*>(sb.buf)[seg * NB + B2];
+            if (need_hi && B2 != 255) M2 = reinterpret_cast<const uint8_t*>(sb.buf)[seg * STRIDE + B2];
             failed = B <= 0 || B >= NB - 1 || (need_hi && (B2 == 255 || B2 >= NB - 1)) || M + M2 > (uint32_t)CAP;
             myinfo = failed ? 0u : ((uint32_t)B | ((need_hi ? (uint32_t)B2 : (uint32_t)B) << 8) | (r << 16) | (n << 24));
         }
