@@ -600,3 +600,34 @@ def test_common_mode_with_massive_ties(torch, kind, mode):
     cal.set_common_mode(cmpars)
     got = cal.calib(_to_dev(torch, raw)).cpu().numpy()
     kat.assert_same_bits(got, _oracle_batch(spec, raw, consts, cmpars), f"{kind} ties mode {mode}")
+
+
+@pytest.mark.parametrize("mode", [4, 2, 7])
+def test_common_mode_windows_follow_offsets_and_spreads(torch, mode):
+    """The medians come from histograms over a WINDOW (64 ADU around the previous frame's median, re-scaled to the spread
+    seen).  Everything that window can get wrong must still end in NumPy's exact median: offsets that jump by hundreds and
+    thousands of ADU from one frame to the next (relocation pass), a bank and columns far from their neighbours (segments that
+    do not fit the tile's window), a bank with noise hundreds of ADU wide (window widening), a bank of constant values."""
+    spec = syn.EPIX10K2M.with_nseg(1)
+    consts = syn.make_constants(spec, seed=410, bad_fraction=0.02)
+    rng = np.random.default_rng(411)
+    nfr = 7
+    base = syn.make_raw_frames(spec, consts, nfr, seed=412).astype(np.int64)
+    gbits = base & 0xC000
+    v = base & 0x3FFF
+    jumps = [0, 300, -2000, 5, 5000, -37, 0]
+    for f in range(nfr):
+        v[f] += jumps[f]
+        v[f, :, :176, 48:96] += 700 * (f % 3)                      # one bank on its own
+        v[f, :, :, 100:103] += 250                                   # three columns on their own
+        v[f, :, 200:352, 192:240] += rng.integers(-600, 600, size=(1, 152, 48))      # a wide bank
+        v[f, :, :176, 336:384] = 3000                                # a constant bank
+    raw = (np.clip(v, 0, 16383) | gbits).astype(np.uint16)
+    cmpars = (7, mode, 1.0e6, 10)
+    cal = _calibrator(spec, consts)
+    cal.set_common_mode(cmpars)
+    got = cal.calib(_to_dev(torch, raw)).cpu().numpy()
+    kat.assert_same_bits(got, _oracle_batch(spec, raw, consts, cmpars), f"windows, mode {mode}")
+    # and the frames one by one (single-frame kernels) give the same
+    one = np.stack([cal.calib(_to_dev(torch, raw[f:f + 1])).cpu().numpy()[0] for f in (1, 4)])
+    kat.assert_same_bits(one, got[[1, 4]], f"single frames, mode {mode}")
