@@ -284,8 +284,20 @@ def measure(torch, du, syn, GpuCalibrator, name, B, steps, warmup, e2e_steps, de
         du.barrier()
         torch.cuda.synchronize()
 
-    h_raw = torch.from_numpy(raw.view(np.int16)).pin_memory()
-    d_raw = h_raw.cuda(non_blocking=True)
+    wc_holder = None
+    if wc_staging:                                    # write-combined pinned staging: the CPU only ever writes the raw frames
+        import ctypes as C
+        from psana_ray import _native as N
+        lib = N.load(); p = C.c_void_p()
+        N.check(lib.psr_host_alloc_wc(C.byref(p), raw.nbytes))
+        wc_holder = (lib, p)
+        h_np = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_int16)), shape=(raw.size,)).reshape(raw.shape)
+        np.copyto(h_np, raw.view(np.int16))
+        h_raw = h_np
+        d_raw = torch.from_numpy(raw.view(np.int16)).cuda()
+    else:
+        h_raw = torch.from_numpy(raw.view(np.int16)).pin_memory()
+        d_raw = h_raw.cuda(non_blocking=True)
     d_out = torch.empty(cal.out_shape(B, image), dtype=torch.float32, device="cuda")
     h_out = torch.empty(cal.out_shape(B, image), dtype=torch.float32).pin_memory()
     stream = torch.cuda.current_stream()
@@ -385,6 +397,9 @@ def measure(torch, du, syn, GpuCalibrator, name, B, steps, warmup, e2e_steps, de
     if clocks is not None:
         res["clocks"] = clocks
     cal.close()
+    if wc_holder is not None:
+        res["e2e"]["staging"] = "write-combined pinned (psr_host_alloc_wc)"
+        wc_holder[0].psr_host_free(wc_holder[1])
     del d_raw, d_out, h_out, h_raw
     torch.cuda.empty_cache()
     return res
@@ -406,6 +421,7 @@ def main():
     ap.add_argument("--also", default="jungfrau,cm,image,image_nocm",
                     help="other BASELINE.json workloads measured into the line's `workloads` object (comma list, '' = none)")
     ap.add_argument("--also-steps", type=int, default=10)
+    ap.add_argument("--wc-staging", action="store_true", help="raw frames staged in write-combined pinned memory (psr_host_alloc_wc)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -446,7 +462,7 @@ def main():
     pcie = pcie_probe(torch, du, world, rank)         # the box's real pinned-copy rates, before anything else loads the links
     e2e_steps = args.e2e_steps or min(args.steps, 20)
     main_res = measure(torch, du, syn, GpuCalibrator, args.workload, args.batch, args.steps, args.warmup, e2e_steps, dev, rank, world,
-                       frames_per_block=args.frames_per_block, sampler=ClockSampler(dev), pcie=pcie)
+                       frames_per_block=args.frames_per_block, sampler=ClockSampler(dev), pcie=pcie, wc_staging=args.wc_staging)
     others = {}
     for name in [w for w in args.also.split(",") if w and w != args.workload]:
         r = measure(torch, du, syn, GpuCalibrator, name, args.batch, args.also_steps, 3, min(args.also_steps, 5), dev, rank, world, pcie=pcie)

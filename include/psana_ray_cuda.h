@@ -172,6 +172,8 @@ int psr_set_host_chunk(psr_ctx* ctx, int chunk_frames, int depth);   /* staging 
 
 /* memory helpers for callers without their own CUDA allocator */
 int psr_host_alloc(void** h_ptr, size_t bytes);          /* pinned */
+int psr_host_alloc_wc(void** h_ptr, size_t bytes);       /* pinned, write-combined: for staging buffers the CPU only writes (raw frames on their way
+                                                           * to the GPU); CPU reads of it are slow.  Free with psr_host_free */
 int psr_host_free(void* h_ptr);
 int psr_host_register(void* h_ptr, size_t bytes);        /* pin an existing buffer */
 int psr_host_unregister(void* h_ptr);

@@ -678,6 +678,11 @@ int psr_host_alloc(void** h_ptr, size_t bytes) {
     PSR_CUDA(cudaHostAlloc(h_ptr, bytes, cudaHostAllocPortable));
     return PSR_OK;
 }
+int psr_host_alloc_wc(void** h_ptr, size_t bytes) {
+    if (!h_ptr) return fail(PSR_E_INVALID, "null h_ptr");
+    PSR_CUDA(cudaHostAlloc(h_ptr, bytes, cudaHostAllocPortable | cudaHostAllocWriteCombined));
+    return PSR_OK;
+}
 int psr_host_free(void* h_ptr) { if (h_ptr) PSR_CUDA(cudaFreeHost(h_ptr)); return PSR_OK; }
 int psr_host_register(void* h_ptr, size_t bytes) {
     if (!h_ptr) return fail(PSR_E_INVALID, "null h_ptr");

@@ -56,6 +56,7 @@ SIGNATURES = {
     "psr_calib_batch_host_wait": (_i, [_vp, _i]),
     "psr_set_host_chunk": (_i, [_vp, _i, _i]),
     "psr_host_alloc": (_i, [_pvp, _sz]),
+    "psr_host_alloc_wc": (_i, [_pvp, _sz]),
     "psr_host_free": (_i, [_vp]),
     "psr_host_register": (_i, [_vp, _sz]),
     "psr_host_unregister": (_i, [_vp]),
