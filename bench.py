@@ -193,6 +193,23 @@ def ncu_traffic(workload):
         return None
 
 
+def workload_config(name, B, world):
+    """The `config` object of the JSON line -- one definition for both arms, so the driver sees the same workload."""
+    from psana_ray import synthetic as syn
+    detector, cmpars, image, cfgname = WORKLOADS[name]
+    spec = syn.detector_spec(detector)
+    image_shape = None
+    if image:
+        iX, iY = syn.make_pixel_index_arrays(spec)
+        image_shape = [int(iX.max()) + 1, int(iY.max()) + 1]
+    out_px = image_shape[0] * image_shape[1] if image else spec.npix
+    return {"workload": cfgname, "detector": spec.name, "frame_shape": list(spec.shape), "batch_per_gpu": B,
+            "common_mode": list(cmpars) if cmpars else None, "image": image_shape,
+            "sharding": "events by rank, no collective" if world > 1 else "single GPU",
+            "l2": f"inputs larger than L2: {2 * spec.npix * B / 1e6:.0f} MB raw in + {4 * out_px * B / 1e6:.0f} MB out per step vs 126 MB L2",
+            "seed": 1000}
+
+
 def reference_arm(args, rank, world):
     if rank != 0:
         return 0
@@ -208,11 +225,11 @@ def reference_arm(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(timed),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": cfgname, "detector": detector, "frames_per_step": frames_per_step,
-                   "note": "reference CPU path = NumPy restatement of psana det.calib (psana/ray/mpi4py not installable offline); "
-                           "one process per host core, mirroring mpirun -n N"},
+        "config": workload_config(args.workload, args.batch, world),
         "cpu_baseline": {"value": value, "unit": "frames/s", "cores": nprocs, "kind": "port",
-                         "sample": f"{frames_per_step} frames per step ({fpp} per process), {len(timed)} timed steps"},
+                         "sample": f"bounded sample of the workload: {frames_per_step} frames per step ({fpp} per process, one process per host core "
+                                   f"like mpirun -n N), {len(timed)} timed steps; reference CPU path = NumPy restatement of psana det.calib "
+                                   "(psana / ray / mpi4py are not installable offline)"},
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -369,11 +386,7 @@ def measure(torch, du, syn, GpuCalibrator, name, B, steps, warmup, e2e_steps, de
     res = {
         "metric": METRIC.replace("epix10k2M", detector), "value": value, "unit": "frames/s", "steps": steps,
         "ms_per_step": total_ms_max / steps,
-        "config": {"workload": cfgname, "detector": spec.name, "frame_shape": list(spec.shape), "batch_per_gpu": B,
-                   "common_mode": list(cmpars) if cmpars else None, "image": image_shape,
-                   "sharding": "events by rank, no collective" if world > 1 else "single GPU",
-                   "l2": f"inputs larger than L2: {raw.nbytes / 1e6:.0f} MB raw in + {d_out.numel() * 4 / 1e6:.0f} MB out per step vs 126 MB L2",
-                   "seed": 1000},
+        "config": workload_config(name, B, world),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": ncu_traffic(name), "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_ms": avg_launch_s * 1e3,

@@ -2,8 +2,10 @@
 //   K1 epix10ka  : gain-bit decode + pedestal + gain + mask          (calib_epix10ka_any)
 //   K2 jungfrau  : gain-bit decode + pedestal + offset + gain + mask (calib_jungfrau,     BASELINE.md 2.3)
 //   K5 masks     : np.where(keep, data, 0) of producer.py:92-95, folded into the epilogues
-//   K4 assemble  : det.image as a gather through the inverse geometry map, either
-//                  fused with K1/K2 (raw -> image directly) or from an already calibrated batch
+//   K4 assemble  : det.image.  Raw -> image directly by SCATTER through the forward map (image_scatter_kernel:
+//                  the map kernels' ownership, every pixel stored where it is the last writer of its target; gaps zeroed by
+//                  img_gap_fill_kernel); from an already calibrated batch by gather through the inverse map (image_gather_kernel);
+//                  image_fused_kernel, the output-driven raw -> image gather, stays selectable as the cross-check
 //   decode       : gain-mode index per pixel, for bit-exact checking of the decode
 //
 // Design: HBM-bound streaming map.  Work is pixel-tile-major, frames-inner: a thread owns a few

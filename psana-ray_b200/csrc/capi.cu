@@ -292,6 +292,9 @@ int psr_create(psr_ctx** out, int det_kind, int nseg, int rows, int cols, int de
 void psr_destroy(psr_ctx* c) {
     if (!c) return;
     DeviceGuard g(c->device);
+    if (c->pipe.s_in) {                              // a batch begun asynchronously may still be using the staging ring
+        cudaStreamSynchronize(c->pipe.s_in); cudaStreamSynchronize(c->pipe.s_comp); cudaStreamSynchronize(c->pipe.s_out);
+    }
     free_pipe(c->pipe);
     if (c->pipe.s_in) cudaStreamDestroy(c->pipe.s_in);
     if (c->pipe.s_comp) cudaStreamDestroy(c->pipe.s_comp);
