@@ -19,6 +19,7 @@
 //     histogram over a linear integer image of the values (their float keys share the high bits and
 //     would all hit the same bins), ties decided by the float keys.
 // Guards (npix_min, cormax) and the eligible-pixels-only subtraction follow UtilsCommonMode.py.
+#include <type_traits>
 #include "psr_kernels.cuh"
 #include "sortnet.cuh"
 
@@ -1373,6 +1374,9 @@ __device__ __noinline__ void rows_sort_phase(const uint32_t* tile, float* cmv, i
 // the groups drift apart and fill each other's barrier and latency gaps, like two CTAs that share their
 // 135 KB of constants.  A thread holds 24 pixels (six 4-pixel chunks) of its group's frame.
 // =================================================================================================
+#ifndef PSR_IMG_ROWOWN   /* image output of the two-group kernel: row ownership on panels rotated by 90 / 270 degrees */
+#define PSR_IMG_ROWOWN 1
+#endif
 template <bool IMG, bool KEEP, bool WORDS, int NG>
 __global__ void __launch_bounds__(704, 1)
 cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c, int nframes, int fpc)
@@ -1398,22 +1402,49 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
     const int tile0 = ((seg * ROWS + half * TR) * COLS) + bank * TC;
 
     for (int i = tid; i < NG * LQ_NB; i += NT) (&hist[0][0])[i] = 0u;
-    // the tile's constants, by all 704 threads; the mask is folded into the gain factors (psr_set_constants)
+    // IMG: is the tile's place in the image t00 + r * dr + c * dc with dr = +-1 for every pixel -- detector rows running
+    // along image rows' x, the panel rotated by 90 / 270 degrees?  Then the threads own the tile differently (below).
+    int rdc = 0;                                                  // dc if so, else 0
+    if constexpr (IMG && PSR_IMG_ROWOWN) {
+        const int t00 = __ldg(c.fwd + tile0), dr = __ldg(c.fwd + tile0 + COLS) - t00, dc = __ldg(c.fwd + tile0 + 1) - t00;
+        bool affine = t00 >= 0 && (dr == 1 || dr == -1);
 #pragma unroll
-    for (int j = 0; j < NCH / NT; ++j) {
-        const int ch = tid + j * NT;
+        for (int j = 0; j < NCH / NT; ++j) {
+            const int ch = tid + j * NT;
+            const int r = ch / CH, cc = ch - r * CH;
+            const int4 a = __ldg(reinterpret_cast<const int4*>(c.fwd + tile0 + r * COLS + cc * 4));
+            const int e = t00 + r * dr + cc * 4 * dc;
+            affine = affine && a.x == e && a.y == e + dc && a.z == e + 2 * dc && a.w == e + 3 * dc;
+        }
+        if (__syncthreads_and(affine ? 1 : 0)) rdc = dc;
+    }
+    // Which chunk is thread tt's j-th.  Normally chunk tt + j * GT: a warp instruction covers 32 consecutive chunks.  On a
+    // rotated tile a warp owns 16 whole tile rows, lane l row l & 15: its chunks 2m, 2m + 1 are the 16 bytes of raw at chunk
+    // 4m + 2 (l >> 4) of that row (one 16-byte load; two lanes share a 32-byte sector), and pixel i of chunk j of lanes 0-15
+    // / 16-31 is 16 consecutive floats of one image row each: stores of 64-byte runs instead of 12-byte ones.
+    auto chunk_of = [&](int tt, int j) {
+        if (IMG && PSR_IMG_ROWOWN && rdc != 0) return ((tt >> 5) * 16 + (tt & 15)) * CH + 4 * (j >> 1) + 2 * ((tt >> 4) & 1) + (j & 1);
+        return tt + j * GT;
+    };
+    // the tile's constants, by all 704 threads, thread-major: [table][j][thread] (whatever the ownership, a warp reads 32
+    // consecutive float4); the mask is folded into the gain factors (psr_set_constants)
+#pragma unroll
+    for (int m = 0; m < NCH / NT; ++m) {
+        const int slot = tid + m * NT;                            // = j * GT + tt
+        const int j = slot / GT, tt = slot - j * GT;
+        const int ch = chunk_of(tt, j);
         const int r = ch / CH, cc = ch - r * CH;
         const int gp = tile0 + r * COLS + cc * 4;
-        sm4[0 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped0 + gp));
-        sm4[1 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.ped1 + gp));
-        sm4[2 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.gf0 + gp));
-        sm4[3 * NCH + ch] = __ldg(reinterpret_cast<const float4*>(c.gf1 + gp));
+        sm4[0 * NCH + slot] = __ldg(reinterpret_cast<const float4*>(c.ped0 + gp));
+        sm4[1 * NCH + slot] = __ldg(reinterpret_cast<const float4*>(c.ped1 + gp));
+        sm4[2 * NCH + slot] = __ldg(reinterpret_cast<const float4*>(c.gf0 + gp));
+        sm4[3 * NCH + slot] = __ldg(reinterpret_cast<const float4*>(c.gf1 + gp));
     }
     uint32_t kbits = 0, e0bits = 0, e1bits = 0;                   // bit BP::pos(i) = value i of this thread
     uint32_t kinds = 0;                                           // IMG: where each chunk goes in the assembled image is the same for every frame
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
-        const int ch = t + j * GT;
+        const int ch = chunk_of(t, j);
         const int r = ch / CH, cc = ch - r * CH;
         const int gp = tile0 + r * COLS + cc * 4;
         if (grp == 0) sgp[j * GT + t] = gp;
@@ -1428,6 +1459,7 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
         }
         if constexpr (IMG) {
             int t0; kinds |= img_chunk_kind<4>(c.fwd + gp, t0) << (2 * j);
+            if (PSR_IMG_ROWOWN && rdc != 0) t0 = __ldg(c.fwd + gp);       // rotated tile: pixel i of the chunk goes to t0 + i * dc
             if (grp == 0) sgp[(CPT + j) * GT + t] = t0;
         }
     }
@@ -1441,6 +1473,9 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
     LqWindow win{LQ_A, 0.5f};                                     // 64 ADU centred on 0, then following the group's medians and their spread
     LqWindow winr{LQ_A, 0.5f}, winc{LQ_A, 0.5f};                  // WORDS: the windows of the row and column histograms
     const SegBuf sb(reinterpret_cast<uint8_t*>(sgp + 2 * CPT * GT) + (WORDS ? grp * SEG_SMEM_BYTES : 0));
+    // the frame loop, compiled twice for images: ROT = the rotated tile's ownership (a tile runs one of the two)
+    auto frames = [&](auto rot_c) {
+    constexpr bool ROT = decltype(rot_c)::value;
     for (int frame = f_begin + grp; frame < f_end; frame += NG) {
         const uint16_t* rawf = raw + (size_t)frame * c.npix;
         float* outf = out + (size_t)frame * fout;
@@ -1448,8 +1483,16 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
         uint32_t sbits = 0;                                       // bit BP::pos(i) = data bit 14 of value i
         if (KEEP) asm volatile("" : "+r"(kbits));                 // not loop-invariant to the compiler: it would hoist (and spill) the single-bit tests
         uint2 rv[CPT];
+        if constexpr (ROT) {                                      // chunks 2m and 2m + 1 are neighbours: one 16-byte load
 #pragma unroll
-        for (int j = 0; j < CPT; ++j) rv[j] = __ldcs(reinterpret_cast<const uint2*>(rawf + sgp[j * GT + t]));
+            for (int m = 0; m < CPT / 2; ++m) {
+                const uint4 v = __ldcs(reinterpret_cast<const uint4*>(rawf + sgp[2 * m * GT + t]));
+                rv[2 * m] = make_uint2(v.x, v.y); rv[2 * m + 1] = make_uint2(v.z, v.w);
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < CPT; ++j) rv[j] = __ldcs(reinterpret_cast<const uint2*>(rawf + sgp[j * GT + t]));
+        }
         if (frame + NG < f_end) {                                 // the group's next raw tile on its way into L2 meanwhile
 #pragma unroll
             for (int j = 0; j < CPT; ++j) asm volatile("prefetch.global.L2 [%0];" :: "l"(rawf + (size_t)NG * c.npix + sgp[j * GT + t]));
@@ -1457,7 +1500,7 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
         uint32_t chain = 0;
 #pragma unroll
         for (int j = 0; j < CPT; ++j) {
-            const int ch = t + j * GT + (int)chain;               // chunk j's pedestals are fetched once chunk j - 1 is done
+            const int ch = t + j * GT + (int)chain;               // (slot in the thread-major tables) chunk j's pedestals are fetched once chunk j - 1 is done
             const uint32_t w[2] = {rv[j].x, rv[j].y};
             const float4 p0 = sm4[0 * NCH + ch], p1 = sm4[1 * NCH + ch];
             const float pa[4] = {p0.x, p0.y, p0.z, p0.w}, pb[4] = {p1.x, p1.y, p1.z, p1.w};
@@ -1546,10 +1589,21 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
             chain = __float_as_uint(o[3]) & zero;
 #endif
             const int gp = sgp[j * GT + t];
-            if constexpr (IMG) img_store_chunk<4>(outf, c.fwd + gp, (kinds >> (2 * j)) & 3u, sgp[(CPT + j) * GT + t], o);
+            if constexpr (IMG) {
+                if constexpr (ROT) {
+                    int idx = sgp[(CPT + j) * GT + t];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) { img_st_at(outf, idx, o[i]); idx += rdc; }
+                } else img_store_chunk<4>(outf, c.fwd + gp, (kinds >> (2 * j)) & 3u, sgp[(CPT + j) * GT + t], o);
+            }
             else __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
         }
     }
+    };
+    if constexpr (IMG && PSR_IMG_ROWOWN) {
+        if (rdc != 0) { frames(std::true_type{}); return; }
+    }
+    frames(std::false_type{});
 }
 
 constexpr int EPIX_NT = 352, JF_NT = 512;
