@@ -1374,6 +1374,9 @@ __device__ __noinline__ void rows_sort_phase(const uint32_t* tile, float* cmv, i
 // the groups drift apart and fill each other's barrier and latency gaps, like two CTAs that share their
 // 135 KB of constants.  A thread holds 24 pixels (six 4-pixel chunks) of its group's frame.
 // =================================================================================================
+#ifndef PSR_IMG_RUNS     /* ... and no per-chunk tests on tiles that are all aligned ascending / descending runs */
+#define PSR_IMG_RUNS 1
+#endif
 #ifndef PSR_IMG_ROWOWN   /* image output of the two-group kernel: row ownership on panels rotated by 90 / 270 degrees */
 #define PSR_IMG_ROWOWN 1
 #endif
@@ -1442,6 +1445,7 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
     }
     uint32_t kbits = 0, e0bits = 0, e1bits = 0;                   // bit BP::pos(i) = value i of this thread
     uint32_t kinds = 0;                                           // IMG: where each chunk goes in the assembled image is the same for every frame
+    bool run_asc = true, run_desc = true, run_a16 = true;
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
         const int ch = chunk_of(t, j);
@@ -1458,10 +1462,18 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
             e1bits |= ((fb & PSR_FL_ELIG1) ? 1u : 0u) << q;
         }
         if constexpr (IMG) {
-            int t0; kinds |= img_chunk_kind<4>(c.fwd + gp, t0) << (2 * j);
+            int t0; const uint32_t kind = img_chunk_kind<4>(c.fwd + gp, t0);
+            kinds |= kind << (2 * j);
+            run_asc = run_asc && kind == 1u && (t0 & 1) == 0; run_desc = run_desc && kind == 2u && (t0 & 1) == 0; run_a16 = run_a16 && (t0 & 3) == 0;
             if (PSR_IMG_ROWOWN && rdc != 0) t0 = __ldg(c.fwd + gp);       // rotated tile: pixel i of the chunk goes to t0 + i * dc
             if (grp == 0) sgp[(CPT + j) * GT + t] = t0;
         }
+    }
+    int runcls = 0; bool al16 = false;                            // see OWN in the frame loop
+    if constexpr (IMG && PSR_IMG_RUNS) {
+        const int na = __syncthreads_and(run_asc ? 1 : 0), nd = __syncthreads_and(run_desc ? 1 : 0);
+        al16 = __syncthreads_and(run_a16 ? 1 : 0) != 0;
+        runcls = na ? 2 : nd ? 3 : 0;
     }
     const size_t fout = IMG ? (size_t)c.H * c.W : (size_t)c.npix;
     // always 0 (this kernel is epix10ka's), but not to the compiler: lets a value be made to depend on another, which
@@ -1474,8 +1486,12 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
     LqWindow winr{LQ_A, 0.5f}, winc{LQ_A, 0.5f};                  // WORDS: the windows of the row and column histograms
     const SegBuf sb(reinterpret_cast<uint8_t*>(sgp + 2 * CPT * GT) + (WORDS ? grp * SEG_SMEM_BYTES : 0));
     // the frame loop, compiled twice for images: ROT = the rotated tile's ownership (a tile runs one of the two)
-    auto frames = [&](auto rot_c) {
-    constexpr bool ROT = decltype(rot_c)::value;
+    auto frames = [&](auto own_c) {
+    // OWN (images): 0 = each chunk by its kind (any geometry), 1 = rotated tile, 2 / 3 = every chunk of the tile is an
+    // ascending / descending run at an 8-byte aligned image index (panel flat or turned by 180 degrees): two 8-byte stores
+    // per chunk, or one of 16 bytes when all of them are 16-byte aligned -- no per-chunk tests in the frame loop
+    constexpr int OWN = decltype(own_c)::value;
+    constexpr bool ROT = OWN == 1;
     for (int frame = f_begin + grp; frame < f_end; frame += NG) {
         const uint16_t* rawf = raw + (size_t)frame * c.npix;
         float* outf = out + (size_t)frame * fout;
@@ -1594,6 +1610,11 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
                     int idx = sgp[(CPT + j) * GT + t];
 #pragma unroll
                     for (int i = 0; i < 4; ++i) { img_st_at(outf, idx, o[i]); idx += rdc; }
+                } else if constexpr (OWN == 2 || OWN == 3) {
+                    float* p = outf + sgp[(CPT + j) * GT + t];
+                    const float q0 = OWN == 2 ? o[0] : o[3], q1 = OWN == 2 ? o[1] : o[2], q2 = OWN == 2 ? o[2] : o[1], q3 = OWN == 2 ? o[3] : o[0];
+                    if (al16) __stcs(reinterpret_cast<float4*>(p), make_float4(q0, q1, q2, q3));
+                    else { __stcs(reinterpret_cast<float2*>(p), make_float2(q0, q1)); __stcs(reinterpret_cast<float2*>(p + 2), make_float2(q2, q3)); }
                 } else img_store_chunk<4>(outf, c.fwd + gp, (kinds >> (2 * j)) & 3u, sgp[(CPT + j) * GT + t], o);
             }
             else __stcs(reinterpret_cast<float4*>(outf + gp), make_float4(o[0], o[1], o[2], o[3]));
@@ -1601,9 +1622,13 @@ cm_banks_epix_groups_kernel(const uint16_t* __restrict__ raw, float* __restrict_
     }
     };
     if constexpr (IMG && PSR_IMG_ROWOWN) {
-        if (rdc != 0) { frames(std::true_type{}); return; }
+        if (rdc != 0) { frames(std::integral_constant<int, 1>{}); return; }
     }
-    frames(std::false_type{});
+    if constexpr (IMG && PSR_IMG_RUNS) {
+        if (runcls == 2) { frames(std::integral_constant<int, 2>{}); return; }
+        if (runcls == 3) { frames(std::integral_constant<int, 3>{}); return; }
+    }
+    frames(std::integral_constant<int, 0>{});
 }
 
 constexpr int EPIX_NT = 352, JF_NT = 512;
