@@ -57,6 +57,12 @@
 #ifndef PSR_LQ_MIN_WINDOW        /* linear median: narrowest window, ADU */
 #define PSR_LQ_MIN_WINDOW 16.0f
 #endif
+#ifndef PSR_CMW_COL_LQ       /* cm_calib_kernel column medians: one-pass quantised histogram per warp, radix select as the fallback */
+#define PSR_CMW_COL_LQ 1
+#endif
+#ifndef PSR_CMW_JF_MINB
+#define PSR_CMW_JF_MINB 1
+#endif
 #ifndef PSR_CM_WORDS_GROUPS       /* epix10ka batches, words with row / column medians: 1 = the two-frame-group kernel, 0 = cm_calib_kernel */
 #define PSR_CM_WORDS_GROUPS 1
 #endif
@@ -280,6 +286,80 @@ __device__ __forceinline__ uint32_t warp_kth_linear(const uint32_t (&key)[NK], i
         if (c <= k) pre = cand;
     }
     return pre;
+}
+
+template <int NB> __device__ __forceinline__ uint32_t lq_bin8(float x, float a, float b);
+// Median of one warp's line (a bank-tile column: lane = row mod 32, NK values per lane) in ONE histogram pass: the values
+// go linearly into 256 bins of a quarter ADU around `centre` (lq_bin8: monotone in x, so the bin of the wanted rank holds
+// the wanted value), the lanes scan the bins, the members of that bin -- a handful -- are ranked against each other as
+// floats.  lo / hi = the two middle order statistics (lo == hi for an odd count).  Returns false, with nothing decided,
+// when the rank falls into an end bin (values outside the window) or the bin holds more than 32 values: the caller then
+// takes the radix select (warp_kth_linear).  n = eligible values of the line (> 0); wh: 256 words of this warp's own.
+template <int NK>
+__device__ __forceinline__ bool warp_median_lq(const float (&x)[NK], uint32_t elig, int n, float centre, uint32_t* wh, float& lo, float& hi)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t waddr = (uint32_t)__cvta_generic_to_shared(wh);
+    const float a = 1.0f / 64.0f, b = __fsub_rn(0.5f, __fmul_rn(centre, a));
+    reinterpret_cast<uint4*>(wh)[2 * lane] = make_uint4(0, 0, 0, 0);
+    reinterpret_cast<uint4*>(wh)[2 * lane + 1] = make_uint4(0, 0, 0, 0);
+    __syncwarp();
+    uint32_t bin[NK];
+#pragma unroll
+    for (int i = 0; i < NK; ++i) {
+        bin[i] = lq_bin8<256>(x[i], a, b);
+        asm volatile("red.shared.add.u32 [%0], %1;" :: "r"(waddr + bin[i] * 4u), "r"((elig >> i) & 1u) : "memory");
+    }
+    __syncwarp();
+    const uint4 b0 = reinterpret_cast<const uint4*>(wh)[2 * lane], b1 = reinterpret_cast<const uint4*>(wh)[2 * lane + 1];
+    const uint32_t cnt[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+    uint32_t sum = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sum += cnt[j];
+    uint32_t incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+    const uint32_t excl = incl - sum, k1 = (uint32_t)(n - 1) >> 1;
+    const bool mine = k1 >= excl && k1 < incl;                       // exactly one lane
+    uint32_t B = 0, r = 0, M = 0;
+    if (mine) {
+        r = k1 - excl; bool done = false;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            if (!done) { if (r < cnt[j]) { B = 8 * lane + j; M = cnt[j]; done = true; } else r -= cnt[j]; }
+    }
+    const int src = __ffs(__ballot_sync(0xFFFFFFFFu, mine)) - 1;
+    B = __shfl_sync(0xFFFFFFFFu, B, src); r = __shfl_sync(0xFFFFFFFFu, r, src); M = __shfl_sync(0xFFFFFFFFu, M, src);
+    if (B == 0u || B == 255u || M > 32u) return false;               // warp-uniform
+    __syncwarp();                                                     // every lane has read its bins: wh becomes the candidate list
+    float* list = reinterpret_cast<float*>(wh);
+    uint32_t base = 0;
+    uint32_t above = KEY_INELIGIBLE;                                  // smallest key beyond the bin (for hi when the bin ends at rank k1)
+#pragma unroll
+    for (int i = 0; i < NK; ++i) {
+        const bool e = (elig >> i) & 1u;
+        const bool hit = e && bin[i] == B;
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, hit);
+        if (hit) list[base + __popc(bal & ((1u << lane) - 1u))] = x[i];
+        base += __popc(bal);
+        if (e && bin[i] > B) above = min(above, psr_f2key(x[i]));
+    }
+    __syncwarp();
+    // rank the M candidates: lane j takes candidate j; ties are ordered by position
+    const float cj = lane < (int)M ? list[lane] : 0.0f;
+    uint32_t rank = 0;
+    for (uint32_t i = 0; i < M; ++i) { const float ci = list[i]; rank += (ci < cj || (ci == cj && (int)i < lane)) ? 1u : 0u; }
+    const uint32_t blo = __ballot_sync(0xFFFFFFFFu, lane < (int)M && rank == r);
+    lo = __shfl_sync(0xFFFFFFFFu, cj, __ffs(blo) - 1);
+    hi = lo;
+    if ((n & 1) == 0) {
+        if (r + 1u < M) {
+            const uint32_t bhi = __ballot_sync(0xFFFFFFFFu, lane < (int)M && rank == r + 1u);
+            hi = __shfl_sync(0xFFFFFFFFu, cj, __ffs(bhi) - 1);
+        } else hi = psr_key2f(__reduce_min_sync(0xFFFFFFFFu, above));
+    }
+    __syncwarp();
+    return true;
 }
 
 // Values of one thread parked in shared memory instead of registers: slot i of thread t at base[i * NT + t]
@@ -673,8 +753,15 @@ __device__ __forceinline__ bool block_median_linear(const X& x, uint32_t elig, i
 
 // smem flag byte of a tile pixel: bit0 mask, bit1 eligible (this frame), bit3 keep, bits 4-5 gain selector
 //   epix10ka selector: data bit 14;  jungfrau selector: 0,1,2 = g0,g1,g2, 3 = none
+// a if p != 0 else b, as one SELP (ptxas turns nested ternaries on the gain bits into branches)
+__device__ __forceinline__ float cm_selp(float a, float b, uint32_t p) {
+    float r;
+    asm("{ .reg .pred q; setp.ne.u32 q, %3, 0; selp.f32 %0, %1, %2, q; }" : "=f"(r) : "f"(a), "f"(b), "r"(p));
+    return r;
+}
+
 template <int DET, int ROWS, int COLS, int NB, int NT>
-__global__ void __launch_bounds__(NT, DET == 0 ? 2 : 1)      // epix10ka: two CTAs/SM (measured: 1.3x on the row medians)
+__global__ void __launch_bounds__(NT, DET == 0 ? 2 : PSR_CMW_JF_MINB)      // epix10ka: two CTAs/SM (measured: 1.3x on the row medians)
 cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDev c)
 {
     constexpr int TR = ROWS / 2, TC = COLS / NB, CH = TC / 8, NCH = TR * CH, CPT = NCH / NT;
@@ -704,9 +791,9 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
     const uint16_t* rawf = raw + (size_t)frame * c.npix;
     float* outf = out + (size_t)frame * c.npix;
     const int mode = c.cm_mode;
+    const bool has_offs = DET != 0 && c.offs != nullptr;
 
     // ---- load: raw + constants -> arrf in smem, keys in registers -------------------------------
-    uint32_t key[CPT * 8];
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
         const int ch = tid + j * NT;
@@ -723,7 +810,7 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
             ld8(c.peds + gp, pa);
             ld8(c.peds + c.npix + gp, pb);
             ld8(c.peds + 2 * (size_t)c.npix + gp, pc);
-            if (c.offs != nullptr) {
+            if (has_offs) {
                 ld8(c.offs + gp, oa);
                 ld8(c.offs + c.npix + gp, ob);
                 ld8(c.offs + 2 * (size_t)c.npix + gp, oc);
@@ -740,25 +827,31 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
                 x = __fsub_rn(x, sel ? pb[i] : pa[i]);
                 elig = sel ? (f & PSR_FL_ELIG1) : (f & PSR_FL_ELIG0);
             } else {
-                const uint32_t gb = v >> 14;
-                sel = gb == 0 ? 0u : gb == 1 ? 1u : gb == 3 ? 2u : 3u;
-                float ped = 0.f, off = 0.f;
-                if (sel == 0) { ped = pa[i]; if (c.offs) off = oa[i]; }
-                else if (sel == 1) { ped = pb[i]; if (c.offs) off = ob[i]; }
-                else if (sel == 2) { ped = pc[i]; if (c.offs) off = oc[i]; }
-                x = __fsub_rn(x, ped);
-                if (c.offs != nullptr) x = __fsub_rn(x, off);
-                elig = (sel < 3 && ((c.elig_mask >> sel) & 1u) && (f & PSR_FL_MASK)) ? 1u : 0u;
+                const uint32_t gb = v >> 14, b0 = gb & 1u, b1 = gb >> 1;     // 00 g0, 01 g1, 11 g2, 10 none
+                sel = gb ^ b1;                                             // 0, 1, 2 = g0, g1, g2; 3 = none
+                x = __fsub_rn(x, cm_selp(cm_selp(pc[i], 0.0f, b0), cm_selp(pb[i], pa[i], b0), b1));
+                if (has_offs) x = __fsub_rn(x, cm_selp(cm_selp(oc[i], 0.0f, b0), cm_selp(ob[i], oa[i], b0), b1));
+                elig = ((c.elig_mask & 7u) >> sel) & ((f & PSR_FL_MASK) ? 1u : 0u);
             }
             const int si = r * ST + cc * 8 + i;
             a[si] = x;
             fl[si] = (uint8_t)((f & (PSR_FL_MASK | PSR_FL_KEEP)) | (elig ? 2u : 0u) | (sel << 4));
-            key[j * 8 + i] = elig ? psr_f2key(x) : KEY_INELIGIBLE;
         }
     }
 
     // ---- mode 4: 2-d median over the whole tile (common_mode_2d: skip if n < npix_min, skip if |cm| > cormax)
     if (mode & 4) {
+        uint32_t key[CPT * 8];                             // the thread's own pixels back from the tile (its own writes: no barrier needed)
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+            const int ch = tid + j * NT;
+            const int r = ch / CH, cc = ch - r * CH;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int si = r * ST + cc * 8 + i;
+                key[j * 8 + i] = (fl[si] & 2u) ? psr_f2key(a[si]) : KEY_INELIGIBLE;
+            }
+        }
         BlockRed<NW> red{redbuf, 0};
         int cnt = 0;
 #pragma unroll
@@ -834,32 +927,44 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
         constexpr int NK = (TR + 31) / 32;
         const int warp = tid >> 5;
         uint32_t* wh = whist + warp * 256;
+        float centre = 0.0f;                                       // of the one-pass window: the warp's previous column's median
         for (int col = warp; col < TC; col += NW) {
-            uint32_t k[NK]; int cnt = 0;
+            float xv[NK]; uint32_t el = 0; int cnt = 0;
 #pragma unroll
             for (int i = 0; i < NK; ++i) {
                 const int r = lane + 32 * i;
-                k[i] = KEY_INELIGIBLE;
-                if (r < TR && (fl[r * ST + col] & 2u)) { k[i] = psr_f2key(a[r * ST + col]); ++cnt; }
+                xv[i] = 0.0f;
+                if (r < TR) {
+                    xv[i] = a[r * ST + col];
+                    if (fl[r * ST + col] & 2u) { el |= 1u << i; ++cnt; }
+                }
             }
             const int n = __reduce_add_sync(0xFFFFFFFFu, cnt);
             if (n > c.npix_min && n > 0) {                         // warp-uniform
-                const uint32_t lo = warp_kth_linear<NK>(k, (n - 1) >> 1, wh);
-                uint32_t hi = lo;
-                if ((n & 1) == 0) {                                // even count: the upper middle value
-                    int cle = 0; uint32_t mg = 0xFFFFFFFFu;
+                float flo, fhi;
+                if (!PSR_CMW_COL_LQ || !warp_median_lq<NK>(xv, el, n, centre, wh, flo, fhi)) {   // rare: values outside the window, or a crowded bin
+                    uint32_t k[NK];
 #pragma unroll
-                    for (int i = 0; i < NK; ++i) { cle += (k[i] <= lo); if (k[i] > lo) mg = min(mg, k[i]); }
-                    cle = __reduce_add_sync(0xFFFFFFFFu, cle);
-                    mg = __reduce_min_sync(0xFFFFFFFFu, mg);
-                    if (cle <= (n >> 1)) hi = mg;
+                    for (int i = 0; i < NK; ++i) k[i] = ((el >> i) & 1u) ? psr_f2key(xv[i]) : KEY_INELIGIBLE;
+                    const uint32_t lo = warp_kth_linear<NK>(k, (n - 1) >> 1, wh);
+                    uint32_t hi = lo;
+                    if ((n & 1) == 0) {                                // even count: the upper middle value
+                        int cle = 0; uint32_t mg = 0xFFFFFFFFu;
+#pragma unroll
+                        for (int i = 0; i < NK; ++i) { cle += (k[i] <= lo); if (k[i] > lo) mg = min(mg, k[i]); }
+                        cle = __reduce_add_sync(0xFFFFFFFFu, cle);
+                        mg = __reduce_min_sync(0xFFFFFFFFu, mg);
+                        if (cle <= (n >> 1)) hi = mg;
+                    }
+                    flo = psr_key2f(lo); fhi = psr_key2f(hi);
                 }
-                const float cm = psr_mid(psr_key2f(lo), psr_key2f(hi));
+                const float cm = psr_mid(flo, fhi);
+                if (fabsf(cm) < 1.0e6f) centre = cm;
                 if (fabsf(cm) < c.cormax) {
 #pragma unroll
                     for (int i = 0; i < NK; ++i) {
                         const int r = lane + 32 * i;
-                        if (k[i] != KEY_INELIGIBLE) a[r * ST + col] = __fsub_rn(a[r * ST + col], cm);
+                        if ((el >> i) & 1u) a[r * ST + col] = __fsub_rn(xv[i], cm);
                     }
                 }
             }
@@ -890,7 +995,7 @@ cm_calib_kernel(const uint16_t* __restrict__ raw, float* __restrict__ out, PsrDe
             const uint32_t sel = f >> 4;
             float gf;
             if (DET == 0) gf = sel ? gb_[i] : ga[i];
-            else gf = sel == 0 ? ga[i] : sel == 1 ? gb_[i] : sel == 2 ? gc[i] : 1.0f;
+            else gf = cm_selp(cm_selp(1.0f, gc[i], sel & 1u), cm_selp(gb_[i], ga[i], sel & 1u), sel >> 1);
             const float v = __fmul_rn(__fmul_rn(a[si], gf), (f & PSR_FL_MASK) ? 1.0f : 0.0f);
             o[i] = (f & PSR_FL_KEEP) ? v : 0.0f;
         }

@@ -25,7 +25,7 @@ ap.add_argument("--cm-mode", type=int, default=4)
 ap.add_argument("--det", default=None)
 ap.add_argument("--npix-min", type=int, default=10)
 ap.add_argument("--gap", type=int, default=10, help="panel gap of the synthetic geometry (image width = f(gap): 10 -> W % 4 == 2, 12 -> W % 4 == 0)")
-ap.add_argument("--geo", default="default", choices=["default", "flat", "rot90", "stack"], help="flat: all panels unrotated in a 2-column stack; rot90: all rotated by 90 degrees")
+ap.add_argument("--geo", default="default", choices=["default", "flat", "rot90", "stack", "col1gap", "col2nogap", "col2pad"], help="flat: all panels unrotated in a 2-column stack; rot90: all rotated by 90 degrees")
 ap.add_argument("--opt", action="append", default=[], help="name=value for psr_set_option, e.g. image_gather=1")
 a = ap.parse_args()
 
@@ -44,6 +44,12 @@ if geo is not None and a.geo != "default":
         pr, pc = divmod(sg, 2)
         if a.geo == "stack":                      # image == calib layout: one column of panels, no gaps
             iX[sg], iY[sg] = r + sg * R, c
+        elif a.geo == "col1gap":                  # one column of panels, gap rows between them
+            iX[sg], iY[sg] = r + sg * (R + a.gap), c
+        elif a.geo == "col2nogap":                # two columns, no gaps at all
+            iX[sg], iY[sg] = r + pr * R, c + pc * Cc
+        elif a.geo == "col2pad":                  # two columns, gap only between the columns (rows contiguous vertically)
+            iX[sg], iY[sg] = r + pr * R, c + pc * (Cc + a.gap)
         elif a.geo == "flat":
             iX[sg], iY[sg] = r + pr * (R + a.gap), c + pc * (Cc + a.gap)
         else:
