@@ -631,3 +631,32 @@ def test_common_mode_windows_follow_offsets_and_spreads(torch, mode):
     # and the frames one by one (single-frame kernels) give the same
     one = np.stack([cal.calib(_to_dev(torch, raw[f:f + 1])).cpu().numpy()[0] for f in (1, 4)])
     kat.assert_same_bits(one, got[[1, 4]], f"single frames, mode {mode}")
+
+
+@pytest.mark.parametrize("mode", [2, 3, 7])
+def test_jungfrau_column_medians_outside_the_histogram_window(torch, mode):
+    """Jungfrau's row / column kernel takes a column's median from ONE 256-bin histogram of a quarter ADU per bin around the
+    warp's previous column median and falls back to a radix select when the rank lands in an end bin or in a crowded bin.
+    Columns hundreds of ADU from their neighbours, columns of constant values (all 256 in one bin), two-valued columns
+    (the upper middle value in a later bin), a bank hundreds of ADU wide and rows with pixels masked out (odd counts) must
+    all end in NumPy's exact median."""
+    spec = syn.JUNGFRAU4M.with_nseg(1)
+    consts = syn.make_constants(spec, seed=420, bad_fraction=0.02)
+    rng = np.random.default_rng(421)
+    nfr = 3
+    base = syn.make_raw_frames(spec, consts, nfr, seed=422).astype(np.int64)
+    gbits = base & 0xC000
+    v = base & 0x3FFF
+    for f in range(nfr):
+        v[f, :, :, 70:73] += 400                                     # three columns far above their bank
+        v[f, :, :256, 130:134] -= 150 * (f + 1)                      # ... and four far below, moving from frame to frame
+        v[f, :, 256:, 192:256] += rng.integers(-500, 500, size=(1, 256, 64))         # a wide bank
+        v[f, :, :256, 320:384] = 2000                                # a constant bank: every column one bin
+        v[f, :, 256:, 448:512] = np.where(rng.random((1, 256, 64)) < 0.5, 1500, 1560)  # two values, 60 ADU apart
+        v[f, :, ::2, 600] += 33                                      # one column split between two far bins
+    raw = (np.clip(v, 0, 16383) | gbits).astype(np.uint16)
+    cmpars = (7, mode, 1.0e6, 10)
+    cal = _calibrator(spec, consts)
+    cal.set_common_mode(cmpars)
+    got = cal.calib(_to_dev(torch, raw)).cpu().numpy()
+    kat.assert_same_bits(got, _oracle_batch(spec, raw, consts, cmpars), f"jungfrau columns, mode {mode}")
