@@ -2,6 +2,8 @@
 """Smallest run that touches every kernel once -- the target for compute-sanitizer (one tool per gpurun call):
     compute-sanitizer --tool racecheck python tools/sanitize_case.py
     compute-sanitizer --tool memcheck  python tools/sanitize_case.py
+(Round 2: compute-sanitizer is closed on the GPU pool; the same case runs plain as a smoke of every kernel, and the parity
+tests' NaN-prefilled outputs and exact comparisons stand in for memcheck.)
 """
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -10,7 +12,7 @@ import numpy as np, torch
 from psana_ray import synthetic as syn
 from psana_ray.calib import GpuCalibrator
 
-for det, nseg in (("epix10k2M", 1), ("jungfrau4M", 1)):
+for det, nseg in (("epix10k2M", 6), ("jungfrau4M", 1)):          # 6 segments: quad 1 is rotated by 90 degrees (the row-owner image epilogue)
     spec = syn.detector_spec(det).with_nseg(nseg)
     consts = syn.make_constants(spec, seed=1, cfg_variant="mixed")
     raw = syn.make_raw_frames(spec, consts, 2, seed=2)
