@@ -1079,7 +1079,7 @@ __device__ __forceinline__ void img_store_chunk(float* __restrict__ imgf, const 
 
 // =================================================================================================
 // mode 4 only (the per-bank 2-d median -- the usual setting): no shared-memory tile at all.  Each
-// thread keeps the keys of its CPT*8 pixels in registers from load to store; eligibility, gain
+// thread keeps the keys of its CPT*CW pixels in registers from load to store; eligibility, gain
 // selector, mask and keep bits are packed in four 32-bit registers.
 // =================================================================================================
 template <int DET, int ROWS, int COLS, int NB, int NT, int MINB, int CW, bool KS, bool IMG>
